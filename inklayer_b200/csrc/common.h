@@ -1,0 +1,32 @@
+// Shared host-side declarations for libinksam: error plumbing and kernel launchers.
+#pragma once
+#include <cuda.h>
+#include <cuda_runtime.h>
+#include <cuda_bf16.h>
+#include <stdint.h>
+#include <stddef.h>
+
+#include "gemm_args.h"
+
+namespace inksam {
+
+// Records a printf-style message retrievable through inksam_last_error(); returns -1.
+int set_error(const char* fmt, ...);
+const char* get_error();
+
+#define CUDA_TRY(expr)                                                                               \
+  do {                                                                                               \
+    cudaError_t _e = (expr);                                                                         \
+    if (_e != cudaSuccess)                                                                           \
+      return ::inksam::set_error("%s:%d: %s -> %s", __FILE__, __LINE__, #expr, cudaGetErrorString(_e)); \
+  } while (0)
+
+#define INK_TRY(expr)            \
+  do {                           \
+    if ((expr) != 0) return -1;  \
+  } while (0)
+
+int launch_gemm(int cg, int tf32, int bn, int epi, const void* A, int lda, const void* W, int ldw, GemmArgs g,
+                int num_sms, cudaStream_t st);
+
+}  // namespace inksam

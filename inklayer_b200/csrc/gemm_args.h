@@ -1,0 +1,36 @@
+// Epilogue selectors and argument block of the tcgen05 GEMM (host-visible, no device code).
+#pragma once
+#include <stdint.h>
+
+namespace inksam {
+
+enum GemmEpi : int {
+  EPI_BIAS_BF16 = 0,       // out_bf16 = acc + bias
+  EPI_BIAS_GELU_BF16 = 1,  // out_bf16 = gelu_erf(acc + bias)
+  EPI_BIAS_RESID_F32 = 2,  // out_f32 = acc + bias + resid                  (resid may alias out)
+  EPI_BIAS_ROWADD_F32 = 3, // out_f32 = acc + bias + rowadd[m % rowadd_mod] (pos_embed / projected PE)
+  EPI_LN_BF16_PAD = 4,     // out_bf16[pad66(m)] = LN_N(acc)       N == BN  (neck conv1x1 + LayerNorm2d)
+  EPI_LN_F32_NCHW = 5,     // out_f32[b][n][tok] = LN_N(acc)       N == BN  (neck conv3x3 + LayerNorm2d)
+  EPI_RESID_LN_F32 = 6,    // out_f32 = LN_N(resid + acc + bias)   N == BN  (decoder keys update, norm4)
+  EPI_BIAS_F32 = 7,        // out_f32 = acc + bias
+  EPI_UPSCALE1 = 8,        // decoder ConvT(256->64,k2,s2)+LayerNorm2d+GELU, out [K][128][128][64] fp32
+  EPI_UPSCALE2_MASK = 9,   // decoder ConvT(64->32,k2,s2)+GELU, dot with hyper_in -> low-res logits
+};
+
+struct GemmArgs {
+  int M, N, K;
+  int ldo;  // output row stride in elements
+  void* out;
+  const float* bias;   // [N] or nullptr
+  const float* resid;  // fp32 [M][ldo]
+  const float* rowadd; // fp32 [rowadd_mod][N]
+  int rowadd_mod;
+  const float* ln_w;
+  const float* ln_b;
+  float ln_eps;
+  int a_conv3x3;       // A is the zero-padded [B][66][66][C] map; K = 9*C (3-D tensor map)
+  int conv_c;
+  const float* hyper;  // EPI_UPSCALE2_MASK: [boxes][32]
+};
+
+}  // namespace inksam

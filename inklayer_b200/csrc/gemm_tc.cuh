@@ -1,0 +1,408 @@
+// Persistent, warp-specialised tcgen05 GEMM for sm_100a.
+//
+//   out[M,N] = epilogue( A[M,K] * W[N,K]^T )      A, W K-major; bf16 (kind::f16) or fp32-as-tf32 (kind::tf32)
+//
+// Structure (one CTA per SM, or one CTA pair per 2 SMs when CG == 2):
+//   warp 0      TMA producer: A/W tiles -> 128B-swizzled smem ring (STAGES deep), mbarrier complete_tx
+//   warp 1      MMA issuer: one thread issues tcgen05.mma (UMMA M = 128*CG, N = BN, K = 32 bytes),
+//               accumulators live in TMEM, double buffered (2 x BN columns)
+//   warp 2      TMEM allocator
+//   warps 4..7  epilogue: tcgen05.ld (thread == output row), fused bias / GELU / residual / LayerNorm,
+//               direct 32-byte vector stores
+//
+// This one kernel replaces every nn.Linear / 1x1 conv / 3x3 conv / conv-transpose GEMM on the hot path:
+//   reference SA/modeling/image_encoder.py:227 (qkv), :238 (proj), common.py:21-26 (MLP),
+//   image_encoder.py:88-104 (neck), :391-395 (patch embed), and the image-side linears of
+//   SA/modeling/transformer.py:218-221 and mask_decoder.py:53-59.
+#pragma once
+#include "ptx.cuh"
+#include "gemm_args.h"
+
+namespace inksam {
+
+__device__ __forceinline__ float gelu_erf(float x) { return 0.5f * x * (1.0f + erff(x * 0.70710678118654752f)); }
+
+__device__ __forceinline__ void tmem_st_32x32(uint32_t taddr, const uint32_t (&r)[32]) {
+  asm volatile(
+      "tcgen05.st.sync.aligned.32x32b.x32.b32 [%0], "
+      "{%1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15, %16, "
+      "%17, %18, %19, %20, %21, %22, %23, %24, %25, %26, %27, %28, %29, %30, %31, %32};" ::"r"(taddr),
+      "r"(r[0]), "r"(r[1]), "r"(r[2]), "r"(r[3]), "r"(r[4]), "r"(r[5]), "r"(r[6]), "r"(r[7]), "r"(r[8]), "r"(r[9]),
+      "r"(r[10]), "r"(r[11]), "r"(r[12]), "r"(r[13]), "r"(r[14]), "r"(r[15]), "r"(r[16]), "r"(r[17]), "r"(r[18]),
+      "r"(r[19]), "r"(r[20]), "r"(r[21]), "r"(r[22]), "r"(r[23]), "r"(r[24]), "r"(r[25]), "r"(r[26]), "r"(r[27]),
+      "r"(r[28]), "r"(r[29]), "r"(r[30]), "r"(r[31])
+      : "memory");
+}
+__device__ __forceinline__ void tmem_st_wait() { asm volatile("tcgen05.wait::st.sync.aligned;" ::: "memory"); }
+
+template <int CG, int TF32, int BN>
+struct GemmCfg {
+  static constexpr int BM = 128;                 // rows per CTA (UMMA M = BM * CG)
+  static constexpr int BNL = BN / CG;            // W rows loaded by each CTA
+  static constexpr int A_BYTES = BM * 128;       // one stage of A: 128 rows x 128 bytes
+  static constexpr int B_BYTES = BNL * 128;
+  static constexpr int STAGE_BYTES = A_BYTES + B_BYTES;
+  static constexpr int STAGES = (192 * 1024) / STAGE_BYTES > 8 ? 8 : (192 * 1024) / STAGE_BYTES;
+  static constexpr int KELEMS = TF32 ? 32 : 64;  // elements per 128-byte smem row
+  static constexpr int SMEM_BYTES = STAGES * STAGE_BYTES + 1024 /*align slack*/ + 256 /*barriers*/;
+  static constexpr uint32_t IDESC = make_idesc(TF32 ? 2u : 1u, BM * CG, BN);
+  static constexpr int TMEM_COLS = 2 * BN;       // double-buffered accumulators (power of two: 256 or 512)
+};
+
+template <int CG, int TF32, int BN, int EPI>
+__global__ void __launch_bounds__(256, 1)
+gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB, const GemmArgs g) {
+  using C = GemmCfg<CG, TF32, BN>;
+  extern __shared__ uint8_t smem_raw[];
+  const uint32_t smem_base = (smem_u32(smem_raw) + 1023u) & ~1023u;
+  const uint32_t bar_base = smem_base + C::STAGES * C::STAGE_BYTES;
+  auto full_bar = [&](int s) { return bar_base + 8u * s; };
+  auto empty_bar = [&](int s) { return bar_base + 8u * (C::STAGES + s); };
+  auto tfull_bar = [&](int s) { return bar_base + 8u * (2 * C::STAGES + s); };
+  auto tempty_bar = [&](int s) { return bar_base + 8u * (2 * C::STAGES + 2 + s); };
+  const uint32_t tmem_slot = bar_base + 8u * (2 * C::STAGES + 4);
+  volatile uint32_t* tmem_slot_ptr =
+      reinterpret_cast<volatile uint32_t*>(smem_raw + (tmem_slot - smem_u32(smem_raw)));
+
+  const int warp = threadIdx.x >> 5;
+  const int lane = threadIdx.x & 31;
+  const uint32_t rank = (CG == 2) ? cluster_ctarank() : 0u;
+  const bool leader = (rank == 0);
+
+  const int tiles_m = (g.M + C::BM * CG - 1) / (C::BM * CG);
+  const int tiles_n = (g.N + BN - 1) / BN;
+  const int num_tiles = tiles_m * tiles_n;
+  const int num_kb = g.a_conv3x3 ? 9 * (g.conv_c / C::KELEMS) : (g.K + C::KELEMS - 1) / C::KELEMS;
+  const int cluster_id = blockIdx.x / CG;
+  const int num_clusters = gridDim.x / CG;
+
+  if (warp == 0 && lane == 0) {
+    tma_prefetch_desc(&tmA);
+    tma_prefetch_desc(&tmB);
+  }
+  if (warp == 1 && lane == 0) {
+    for (int s = 0; s < C::STAGES; ++s) {
+      mbar_init(full_bar(s), CG);  // CG == 2: leader's expect_tx arrive + peer's plain arrive
+      mbar_init(empty_bar(s), 1);  // one tcgen05.commit
+    }
+    for (int s = 0; s < 2; ++s) {
+      mbar_init(tfull_bar(s), 1);          // one tcgen05.commit
+      mbar_init(tempty_bar(s), 128 * CG);  // every epilogue thread of the pair
+    }
+    fence_mbar_init();
+  }
+  if (warp == 2) {
+    tmem_alloc<CG>(tmem_slot, C::TMEM_COLS);
+    tmem_relinquish<CG>();
+  }
+  tc_fence_before();
+  if constexpr (CG == 2) cluster_sync_all(); else __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem_base = *tmem_slot_ptr;
+
+  if (warp == 0) {
+    // ------------------------------------------------------------ TMA producer
+    if (lane == 0) {
+      int stage = 0;
+      uint32_t phase = 0;
+      for (int tile = cluster_id; tile < num_tiles; tile += num_clusters) {
+        const int m_blk = tile / tiles_n, n_blk = tile % tiles_n;
+        const int m0 = m_blk * C::BM * CG + (int)rank * C::BM;
+        const int n0 = n_blk * BN + (int)rank * C::BNL;
+        for (int kb = 0; kb < num_kb; ++kb) {
+          mbar_wait(empty_bar(stage), phase ^ 1u);
+          const uint32_t a_dst = smem_base + stage * C::STAGE_BYTES;
+          const uint32_t b_dst = a_dst + C::A_BYTES;
+          const int k0 = kb * C::KELEMS;
+          if constexpr (CG == 1) {
+            mbar_arrive_expect_tx(full_bar(stage), C::STAGE_BYTES);
+            if (g.a_conv3x3) {
+              const int cpt = g.conv_c / C::KELEMS;  // k-blocks per filter tap
+              const int tap = kb / cpt, c0 = (kb % cpt) * C::KELEMS;
+              const int b = m0 >> 12, y0 = (m0 & 4095) >> 6;
+              tma_load_3d(a_dst, &tmA, full_bar(stage), c0, tap % 3, b * 66 + y0 + tap / 3);
+            } else {
+              tma_load_2d(a_dst, &tmA, full_bar(stage), k0, m0);
+            }
+            tma_load_2d(b_dst, &tmB, full_bar(stage), k0, n0);
+          } else {
+            const uint32_t lead_full = mapa_u32(full_bar(stage), 0);
+            if (leader) mbar_arrive_expect_tx(full_bar(stage), 2 * C::STAGE_BYTES);
+            else mbar_arrive_cluster(lead_full);
+            if (g.a_conv3x3) {
+              const int cpt = g.conv_c / C::KELEMS;
+              const int tap = kb / cpt, c0 = (kb % cpt) * C::KELEMS;
+              const int b = m0 >> 12, y0 = (m0 & 4095) >> 6;
+              tma_load_3d_cg2(a_dst, &tmA, lead_full, c0, tap % 3, b * 66 + y0 + tap / 3);
+            } else {
+              tma_load_2d_cg2(a_dst, &tmA, lead_full, k0, m0);
+            }
+            tma_load_2d_cg2(b_dst, &tmB, lead_full, k0, n0);
+          }
+          if (++stage == C::STAGES) { stage = 0; phase ^= 1u; }
+        }
+      }
+    }
+    __syncwarp();
+  } else if (warp == 1) {
+    // ------------------------------------------------------------ MMA issuer (pair leader only)
+    if (lane == 0 && leader) {
+      int stage = 0;
+      uint32_t phase = 0;
+      int as = 0;
+      uint32_t aphase = 0;
+      for (int tile = cluster_id; tile < num_tiles; tile += num_clusters) {
+        mbar_wait_cluster(tempty_bar(as), aphase ^ 1u);  // epilogue has drained this accumulator
+        tc_fence_after();
+        const uint32_t d_tmem = tmem_base + (uint32_t)(as * BN);
+        for (int kb = 0; kb < num_kb; ++kb) {
+          mbar_wait(full_bar(stage), phase);
+          tc_fence_after();
+          const uint32_t a_addr = smem_base + stage * C::STAGE_BYTES;
+          const uint64_t adesc = make_kmajor_sw128_desc(a_addr);
+          const uint64_t bdesc = make_kmajor_sw128_desc(a_addr + C::A_BYTES);
+#pragma unroll
+          for (int k = 0; k < 4; ++k)  // 4 x 32 bytes of K per 128-byte swizzled row
+            umma<CG, TF32>(d_tmem, adesc + 2u * k, bdesc + 2u * k, C::IDESC, (uint32_t)((kb | k) != 0));
+          umma_commit<CG>(empty_bar(stage));  // smem slot free once these MMAs retire
+          if (++stage == C::STAGES) { stage = 0; phase ^= 1u; }
+        }
+        umma_commit<CG>(tfull_bar(as));  // accumulator complete -> epilogue
+        if (++as == 2) { as = 0; aphase ^= 1u; }
+      }
+    }
+    __syncwarp();
+  } else if (warp >= 4) {
+    // ------------------------------------------------------------ epilogue (thread == output row)
+    const int q = warp & 3;  // TMEM sub-partition this warp may read: lanes [32q, 32q+32)
+    int as = 0;
+    uint32_t aphase = 0;
+    for (int tile = cluster_id; tile < num_tiles; tile += num_clusters) {
+      const int m_blk = tile / tiles_n, n_blk = tile % tiles_n;
+      const int m = m_blk * C::BM * CG + (int)rank * C::BM + q * 32 + lane;
+      const int n0 = n_blk * BN;
+      const bool row_ok = m < g.M;
+      mbar_wait(tfull_bar(as), aphase);
+      tc_fence_after();
+      const uint32_t taddr = tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)(as * BN);
+      constexpr int NCH = BN / 32;
+
+      if constexpr (EPI == EPI_BIAS_BF16 || EPI == EPI_BIAS_GELU_BF16 || EPI == EPI_BIAS_RESID_F32 ||
+                    EPI == EPI_BIAS_ROWADD_F32 || EPI == EPI_BIAS_F32) {
+        uint32_t v[2][32];
+        tmem_ld_32x32(taddr, v[0]);
+#pragma unroll
+        for (int c = 0; c < NCH; ++c) {
+          const int col = n0 + c * 32;
+          tmem_ld_wait();
+          if (c + 1 < NCH) tmem_ld_32x32(taddr + (c + 1) * 32, v[(c + 1) & 1]);
+          if (col < g.N) {
+            float* f = reinterpret_cast<float*>(v[c & 1]);
+            if (g.bias != nullptr) {
+#pragma unroll
+              for (int j = 0; j < 32; j += 4) {
+                const float4 b4 = __ldg(reinterpret_cast<const float4*>(g.bias + col + j));
+                f[j] += b4.x; f[j + 1] += b4.y; f[j + 2] += b4.z; f[j + 3] += b4.w;
+              }
+            }
+            if constexpr (EPI == EPI_BIAS_GELU_BF16) {
+#pragma unroll
+              for (int j = 0; j < 32; ++j) f[j] = gelu_erf(f[j]);
+            }
+            if constexpr (EPI == EPI_BIAS_BF16 || EPI == EPI_BIAS_GELU_BF16) {
+              if (row_ok) {
+                __nv_bfloat16* o = reinterpret_cast<__nv_bfloat16*>(g.out) + (size_t)m * g.ldo + col;
+#pragma unroll
+                for (int h = 0; h < 2; ++h) {
+                  uint32_t pk[8];
+#pragma unroll
+                  for (int j = 0; j < 8; ++j) pk[j] = pack_bf16x2(f[h * 16 + 2 * j], f[h * 16 + 2 * j + 1]);
+                  st_global_v8(o + h * 16, pk);
+                }
+              }
+            } else {
+              if (row_ok) {
+                float* o = reinterpret_cast<float*>(g.out) + (size_t)m * g.ldo + col;
+                const float* add = nullptr;
+                if constexpr (EPI == EPI_BIAS_RESID_F32) add = g.resid + (size_t)m * g.ldo + col;
+                if constexpr (EPI == EPI_BIAS_ROWADD_F32) add = g.rowadd + (size_t)(m % g.rowadd_mod) * g.N + col;
+#pragma unroll
+                for (int h = 0; h < 4; ++h) {
+                  uint32_t pk[8];
+                  if constexpr (EPI != EPI_BIAS_F32) {
+                    ld_global_v8(add + h * 8, pk);
+#pragma unroll
+                    for (int j = 0; j < 8; ++j) pk[j] = __float_as_uint(__uint_as_float(pk[j]) + f[h * 8 + j]);
+                  } else {
+#pragma unroll
+                    for (int j = 0; j < 8; ++j) pk[j] = __float_as_uint(f[h * 8 + j]);
+                  }
+                  st_global_v8(o + h * 8, pk);
+                }
+              }
+            }
+          }
+        }
+      } else if constexpr (EPI == EPI_LN_BF16_PAD || EPI == EPI_LN_F32_NCHW || EPI == EPI_RESID_LN_F32) {
+        // LayerNorm over the N == BN columns of this thread's row; the row lives in TMEM, so the three
+        // passes (mean, variance, normalise) re-read TMEM instead of holding 256 registers.
+        uint32_t v[32];
+        float* f = reinterpret_cast<float*>(v);
+        float sum = 0.f;
+#pragma unroll 1
+        for (int c = 0; c < NCH; ++c) {
+          tmem_ld_32x32(taddr + c * 32, v);
+          tmem_ld_wait();
+          if constexpr (EPI == EPI_RESID_LN_F32) {
+            const int mm = row_ok ? m : 0;
+            const float* r = g.resid + (size_t)mm * g.ldo + c * 32;
+#pragma unroll
+            for (int h = 0; h < 4; ++h) {
+              uint32_t pk[8];
+              ld_global_v8(r + h * 8, pk);
+#pragma unroll
+              for (int j = 0; j < 8; ++j) f[h * 8 + j] += __uint_as_float(pk[j]) + __ldg(g.bias + c * 32 + h * 8 + j);
+            }
+            tmem_st_32x32(taddr + c * 32, v);  // keep resid + acc + bias in TMEM for the next passes
+          }
+#pragma unroll
+          for (int j = 0; j < 32; ++j) sum += f[j];
+        }
+        if constexpr (EPI == EPI_RESID_LN_F32) tmem_st_wait();
+        const float mean = sum * (1.0f / BN);
+        float sq = 0.f;
+#pragma unroll 1
+        for (int c = 0; c < NCH; ++c) {
+          tmem_ld_32x32(taddr + c * 32, v);
+          tmem_ld_wait();
+#pragma unroll
+          for (int j = 0; j < 32; ++j) { const float d = f[j] - mean; sq += d * d; }
+        }
+        const float rstd = rsqrtf(sq * (1.0f / BN) + g.ln_eps);
+#pragma unroll 1
+        for (int c = 0; c < NCH; ++c) {
+          tmem_ld_32x32(taddr + c * 32, v);
+          tmem_ld_wait();
+#pragma unroll
+          for (int j = 0; j < 32; ++j)
+            f[j] = (f[j] - mean) * rstd * __ldg(g.ln_w + c * 32 + j) + __ldg(g.ln_b + c * 32 + j);
+          if (row_ok) {
+            if constexpr (EPI == EPI_LN_BF16_PAD) {
+              // token m = (b, y, x) -> row (b*66 + y+1)*66 + x+1 of the zero-bordered map
+              const int b = m >> 12, y = (m >> 6) & 63, x = m & 63;
+              __nv_bfloat16* o = reinterpret_cast<__nv_bfloat16*>(g.out) +
+                                 ((size_t)(b * 66 + y + 1) * 66 + x + 1) * g.ldo + c * 32;
+#pragma unroll
+              for (int h = 0; h < 2; ++h) {
+                uint32_t pk[8];
+#pragma unroll
+                for (int j = 0; j < 8; ++j) pk[j] = pack_bf16x2(f[h * 16 + 2 * j], f[h * 16 + 2 * j + 1]);
+                st_global_v8(o + h * 16, pk);
+              }
+            } else if constexpr (EPI == EPI_LN_F32_NCHW) {
+              // out[b][n][tok]: consecutive lanes are consecutive tokens -> coalesced per channel
+              const int b = m >> 12, tok = m & 4095;
+              float* o = reinterpret_cast<float*>(g.out) + ((size_t)b * BN + c * 32) * 4096 + tok;
+#pragma unroll
+              for (int j = 0; j < 32; ++j) o[(size_t)j * 4096] = f[j];
+            } else {
+              float* o = reinterpret_cast<float*>(g.out) + (size_t)m * g.ldo + c * 32;
+#pragma unroll
+              for (int h = 0; h < 4; ++h) {
+                uint32_t pk[8];
+#pragma unroll
+                for (int j = 0; j < 8; ++j) pk[j] = __float_as_uint(f[h * 8 + j]);
+                st_global_v8(o + h * 8, pk);
+              }
+            }
+          }
+        }
+      } else if constexpr (EPI == EPI_UPSCALE1) {
+        // Columns are (dy,dx,o): 4 sub-pixels x 64 channels. LayerNorm2d over o per sub-pixel, then GELU.
+        // Row m = (box, y, x) of the 64x64 grid; output pixel (2y+dy, 2x+dx) of a [box][128][128][64] map.
+        static_assert(EPI != EPI_UPSCALE1 || BN == 256, "upscale1 needs BN == 256");
+        uint32_t v[2][32];
+        const int bx = m >> 12, y = (m >> 6) & 63, x = m & 63;
+#pragma unroll 1
+        for (int sp = 0; sp < 4; ++sp) {
+          float* f0 = reinterpret_cast<float*>(v[0]);
+          float* f1 = reinterpret_cast<float*>(v[1]);
+          tmem_ld_32x32(taddr + sp * 64, v[0]);
+          tmem_ld_32x32(taddr + sp * 64 + 32, v[1]);
+          tmem_ld_wait();
+          float sum = 0.f;
+#pragma unroll
+          for (int j = 0; j < 32; ++j) {
+            f0[j] += __ldg(g.bias + j);
+            f1[j] += __ldg(g.bias + 32 + j);
+            sum += f0[j] + f1[j];
+          }
+          const float mean = sum * (1.0f / 64);
+          float sq = 0.f;
+#pragma unroll
+          for (int j = 0; j < 32; ++j) {
+            const float d0 = f0[j] - mean, d1 = f1[j] - mean;
+            sq += d0 * d0 + d1 * d1;
+          }
+          const float rstd = rsqrtf(sq * (1.0f / 64) + g.ln_eps);
+#pragma unroll
+          for (int j = 0; j < 32; ++j) {
+            f0[j] = gelu_erf((f0[j] - mean) * rstd * __ldg(g.ln_w + j) + __ldg(g.ln_b + j));
+            f1[j] = gelu_erf((f1[j] - mean) * rstd * __ldg(g.ln_w + 32 + j) + __ldg(g.ln_b + 32 + j));
+          }
+          if (row_ok) {
+            const int Y = 2 * y + (sp >> 1), X = 2 * x + (sp & 1);
+            float* o = reinterpret_cast<float*>(g.out) + (((size_t)bx * 128 + Y) * 128 + X) * 64;
+#pragma unroll
+            for (int h = 0; h < 4; ++h) {
+              uint32_t pk[8];
+#pragma unroll
+              for (int j = 0; j < 8; ++j) pk[j] = v[0][h * 8 + j];
+              st_global_v8(o + h * 8, pk);
+#pragma unroll
+              for (int j = 0; j < 8; ++j) pk[j] = v[1][h * 8 + j];
+              st_global_v8(o + 32 + h * 8, pk);
+            }
+          }
+        }
+      } else if constexpr (EPI == EPI_UPSCALE2_MASK) {
+        // Columns are (dy,dx,o): 4 sub-pixels x 32 channels; GELU then dot with the box's hypernetwork
+        // vector (mask token 0) -> one low-res logit per sub-pixel. Row m = (box, Y, X) of the 128x128 map.
+        static_assert(EPI != EPI_UPSCALE2_MASK || BN == 128, "upscale2 needs BN == 128");
+        uint32_t v[32];
+        float* f = reinterpret_cast<float*>(v);
+        const int mm = row_ok ? m : 0;
+        const int bx = mm >> 14, Y = (mm >> 7) & 127, X = mm & 127;
+        const float* hy = g.hyper + (size_t)bx * 32;
+        float logit[4];
+#pragma unroll
+        for (int sp = 0; sp < 4; ++sp) {
+          tmem_ld_32x32(taddr + sp * 32, v);
+          tmem_ld_wait();
+          float acc = 0.f;
+#pragma unroll
+          for (int j = 0; j < 32; ++j) acc += gelu_erf(f[j] + __ldg(g.bias + j)) * __ldg(hy + j);
+          logit[sp] = acc;
+        }
+        if (row_ok) {
+          float* o = reinterpret_cast<float*>(g.out) + ((size_t)bx * 256 + 2 * Y) * 256 + 2 * X;
+          *reinterpret_cast<float2*>(o) = make_float2(logit[0], logit[1]);
+          *reinterpret_cast<float2*>(o + 256) = make_float2(logit[2], logit[3]);
+        }
+      }
+
+      tc_fence_before();
+      if constexpr (CG == 1) mbar_arrive(tempty_bar(as));
+      else mbar_arrive_cluster(mapa_u32(tempty_bar(as), 0));
+      if (++as == 2) { as = 0; aphase ^= 1u; }
+    }
+  }
+
+  // ---------------------------------------------------------------- teardown
+  tc_fence_before();
+  if constexpr (CG == 2) cluster_sync_all(); else __syncthreads();
+  tc_fence_after();
+  if (warp == 2) tmem_dealloc<CG>(tmem_base, C::TMEM_COLS);
+}
+
+}  // namespace inksam
