@@ -1,0 +1,52 @@
+"""Pins oracle/sam_oracle.py to the reference: golden vectors in tests/golden/*.npz were produced by the
+unmodified vendored segment_anything (tests/golden/make_golden.py).  fp32 on both sides, so the only
+difference is summation order: tolerances are a few ulp-scale multiples, masks must match bit for bit
+except where a logit sits within that noise of zero."""
+import numpy as np
+import pytest
+import torch
+
+from conftest import golden_case_inputs, load_golden, mask_iou
+from inklayer_b200.weights import synthetic_state_dict
+from oracle import sam_oracle as O
+
+
+@pytest.mark.parametrize("case", ["tiny_1024", "tiny80_600x750", "vit_b_750_bunny", "vit_h_1024"])
+def test_oracle_matches_reference_golden(case):
+    cfg_name, seed, img, boxes = golden_case_inputs(case)
+    gold = load_golden(case)
+    np.testing.assert_array_equal(boxes, gold["boxes"])
+    cfg = O.CONFIGS[cfg_name]
+    from inklayer_b200.config import CONFIGS
+
+    pred = O.OraclePredictor(cfg, synthetic_state_dict(CONFIGS[cfg_name], seed))
+    pred.set_image(img)
+    tb = O.apply_boxes(torch.from_numpy(boxes), img.shape[:2])
+    np.testing.assert_allclose(tb.numpy(), gold["boxes_input_frame"], rtol=0, atol=0)
+    masks, iou, low = pred.predict_torch(tb)
+    emb = pred.features[0].numpy()
+    np.testing.assert_allclose(emb[:, ::4, ::4], gold["emb_sub"], atol=2e-4, rtol=0)
+    assert abs(np.abs(emb.astype(np.float64)).sum() - gold["emb_abs_sum"]) / gold["emb_abs_sum"] < 1e-5
+    np.testing.assert_allclose(low.numpy()[:, :, ::4, ::4], gold["low_sub"], atol=2e-5, rtol=0)
+    np.testing.assert_allclose(iou.numpy(), gold["iou"], atol=1e-5, rtol=0)
+    ref_masks = np.unpackbits(gold["mask_bits"])[: int(np.prod(gold["mask_shape"]))].reshape(gold["mask_shape"])
+    assert mask_iou(masks[:4].numpy(), ref_masks).min() > 0.9999
+    np.testing.assert_allclose(masks.flatten(1).sum(1).numpy(), gold["mask_area"], rtol=2e-4)
+
+
+def test_oracle_error_convention():
+    """SA/predictor.py:213-214: predicting before set_image raises RuntimeError."""
+    cfg = O.CONFIGS["vit_tiny"]
+    from inklayer_b200.config import CONFIGS
+
+    pred = O.OraclePredictor(cfg, synthetic_state_dict(CONFIGS["vit_tiny"], 0))
+    with pytest.raises(RuntimeError):
+        pred.predict_torch(torch.zeros(1, 4))
+
+
+def test_preprocess_shape_rounding():
+    """SA/utils/transforms.py:93-102."""
+    assert O.preprocess_shape(750, 750, 1024) == (1024, 1024)
+    assert O.preprocess_shape(600, 750, 1024) == (819, 1024)
+    assert O.preprocess_shape(1024, 512, 1024) == (1024, 512)
+    assert O.preprocess_shape(333, 1000, 1024) == (341, 1024)
