@@ -1,0 +1,74 @@
+// Host side of the encoder attention kernels: tensor maps over the qkv matrix and the rel-pos table, launch.
+#include "common.h"
+#include "attn_tc.cuh"
+
+namespace inksam {
+
+template <int HD>
+static int launch_global(const __nv_bfloat16* qkv, const __nv_bfloat16* rel, const AttnArgs& a, cudaStream_t st) {
+  CUtensorMap tm64, tm16, tr64, tr16;
+  const uint64_t rows = (uint64_t)a.B * 4096, cols = 3ull * a.D;
+  INK_TRY(make_tmap_bf16_box(&tm64, qkv, rows, cols, cols, 64, 128));
+  INK_TRY(make_tmap_bf16_box(&tr64, rel, 256, HD, HD, 64, 128));
+  if (HD == 80) {
+    INK_TRY(make_tmap_bf16_box(&tm16, qkv, rows, cols, cols, 16, 128));
+    INK_TRY(make_tmap_bf16_box(&tr16, rel, 256, HD, HD, 16, 128));
+  } else {
+    tm16 = tm64; tr16 = tr64;
+  }
+  constexpr int SMEM = 3 * AttnTile<HD>::bytes(128) + 128 * 66 * 4 + 64 + 1024;
+  auto kern = attn_global_kernel<HD>;
+  static bool attr_done = false;
+  if (!attr_done) {
+    CUDA_TRY(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM));
+    attr_done = true;
+  }
+  kern<<<a.B * a.heads * 32, 128, SMEM, st>>>(tm64, tm16, tr64, tr16, a);
+  CUDA_TRY(cudaGetLastError());
+  return 0;
+}
+
+template <int HD>
+static int launch_window(const __nv_bfloat16* qkv, const __nv_bfloat16* rel, const AttnArgs& a, cudaStream_t st) {
+  CUtensorMap tq64, tq16, tk64, tk16, tr64, tr16;
+  const uint64_t rows = (uint64_t)a.B * 25 * 196, cols = 3ull * a.D;
+  INK_TRY(make_tmap_bf16_box(&tq64, qkv, rows, cols, cols, 64, 128));
+  INK_TRY(make_tmap_bf16_box(&tk64, qkv, rows, cols, cols, 64, 208));
+  INK_TRY(make_tmap_bf16_box(&tr64, rel, 64, HD, HD, 64, 64));
+  if (HD == 80) {
+    INK_TRY(make_tmap_bf16_box(&tq16, qkv, rows, cols, cols, 16, 128));
+    INK_TRY(make_tmap_bf16_box(&tk16, qkv, rows, cols, cols, 16, 208));
+    INK_TRY(make_tmap_bf16_box(&tr16, rel, 64, HD, HD, 16, 64));
+  } else {
+    tq16 = tq64; tk16 = tk64; tr16 = tr64;
+  }
+  constexpr int KT = AttnTile<HD>::bytes(208);
+  constexpr int VBUF = KT > 33280 ? KT : 33792;
+  constexpr int SMEM = AttnTile<HD>::bytes(128) + KT + VBUF + 64 + 1024;
+  auto kern = attn_window_kernel<HD>;
+  static bool attr_done = false;
+  if (!attr_done) {
+    CUDA_TRY(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM));
+    attr_done = true;
+  }
+  kern<<<a.B * 25 * a.heads * 2, 128, SMEM, st>>>(tq64, tq16, tk64, tk16, tr64, tr16, a);
+  CUDA_TRY(cudaGetLastError());
+  return 0;
+}
+
+// qkv: bf16 [rows][3D] (natural order for global blocks, window order for windowed blocks);
+// rel: bf16 rel-pos table ([256][hd] global, [64][hd] windowed); out: bf16 [B*4096][D].
+int launch_attention(int windowed, const void* qkv, const void* rel, void* out, int B, int heads, int head_dim,
+                     cudaStream_t st) {
+  AttnArgs a;
+  a.B = B; a.heads = heads; a.D = heads * head_dim;
+  a.c1 = (1.0f / sqrtf((float)head_dim)) * kLog2e;
+  a.out = static_cast<__nv_bfloat16*>(out);
+  const auto* q = static_cast<const __nv_bfloat16*>(qkv);
+  const auto* r = static_cast<const __nv_bfloat16*>(rel);
+  if (head_dim == 80) return windowed ? launch_window<80>(q, r, a, st) : launch_global<80>(q, r, a, st);
+  if (head_dim == 64) return windowed ? launch_window<64>(q, r, a, st) : launch_global<64>(q, r, a, st);
+  return set_error("attention: head_dim %d not supported (64 or 80)", head_dim);
+}
+
+}  // namespace inksam

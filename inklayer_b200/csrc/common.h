@@ -26,6 +26,9 @@ const char* get_error();
     if ((expr) != 0) return -1;  \
   } while (0)
 
+int make_tmap_bf16_box(CUtensorMap* out, const void* base, uint64_t rows, uint64_t cols, uint64_t ld_elems,
+                       uint32_t box_cols, uint32_t box_rows);
+
 int launch_gemm(int cg, int tf32, int bn, int epi, const void* A, int lda, const void* W, int ldw, GemmArgs g,
                 int num_sms, cudaStream_t st);
 

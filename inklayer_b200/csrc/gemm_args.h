@@ -31,6 +31,8 @@ struct GemmArgs {
   int a_conv3x3;       // A is the zero-padded [B][66][66][C] map; K = 9*C (3-D tensor map)
   int conv_c;
   const float* hyper;  // EPI_UPSCALE2_MASK: [boxes][32]
+  int win_remap;       // EPI_BIAS_BF16: store token rows in 14x14-window order (windowed encoder blocks)
+  int resid_mod;       // EPI_RESID_LN_F32: resid row = m % resid_mod when non-zero (keys shared by all boxes)
 };
 
 }  // namespace inksam

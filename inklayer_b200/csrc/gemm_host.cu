@@ -39,6 +39,24 @@ int make_tmap_2d(CUtensorMap* out, const void* base, int elem_bytes, uint64_t ro
   return 0;
 }
 
+// bf16 row-major [rows][cols] matrix, arbitrary box; swizzle 128B (box_cols == 64) or 32B (box_cols == 16).
+int make_tmap_bf16_box(CUtensorMap* out, const void* base, uint64_t rows, uint64_t cols, uint64_t ld_elems,
+                       uint32_t box_cols, uint32_t box_rows) {
+  if (fetch_encode()) return set_error("cuTensorMapEncodeTiled entry point not available");
+  cuuint64_t dims[2] = {cols, rows};
+  cuuint64_t strides[1] = {ld_elems * 2};
+  cuuint32_t box[2] = {box_cols, box_rows};
+  cuuint32_t estr[2] = {1, 1};
+  const CUtensorMapSwizzle sw = box_cols == 64 ? CU_TENSOR_MAP_SWIZZLE_128B : CU_TENSOR_MAP_SWIZZLE_32B;
+  CUresult r = g_encode(out, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2, const_cast<void*>(base), dims, strides, box, estr,
+                        CU_TENSOR_MAP_INTERLEAVE_NONE, sw, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
+                        CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+  if (r != CUDA_SUCCESS) return set_error("cuTensorMapEncodeTiled(box %ux%u) failed: %d (rows=%llu cols=%llu ld=%llu)",
+                                          box_cols, box_rows, (int)r, (unsigned long long)rows,
+                                          (unsigned long long)cols, (unsigned long long)ld_elems);
+  return 0;
+}
+
 // Zero-bordered channels-last map [nb*66][66][C] bf16 for the 3x3 conv; box = 64 channels x 64 x 2 rows.
 int make_tmap_conv3(CUtensorMap* out, const void* base, int nb, int C) {
   if (fetch_encode()) return set_error("cuTensorMapEncodeTiled entry point not available");
@@ -122,6 +140,10 @@ int launch_gemm(int cg, int tf32, int bn, int epi, const void* A, int lda, const
   GEMM_CASE(2, 1, 256, EPI_RESID_LN_F32)
   GEMM_CASE(1, 1, 256, EPI_UPSCALE1)
   GEMM_CASE(2, 1, 256, EPI_UPSCALE1)
+  GEMM_CASE(1, 1, 128, EPI_BIAS_F32)
+  GEMM_CASE(2, 1, 128, EPI_BIAS_F32)
+  GEMM_CASE(1, 1, 128, EPI_BIAS_ROWADD_F32)
+  GEMM_CASE(2, 1, 128, EPI_BIAS_ROWADD_F32)
   GEMM_CASE(1, 1, 128, EPI_UPSCALE2_MASK)
   GEMM_CASE(2, 1, 128, EPI_UPSCALE2_MASK)
   return set_error("gemm: no kernel for cg=%d tf32=%d bn=%d epi=%d", cg, tf32, bn, epi);

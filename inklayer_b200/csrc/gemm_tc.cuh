@@ -22,19 +22,6 @@ namespace inksam {
 
 __device__ __forceinline__ float gelu_erf(float x) { return 0.5f * x * (1.0f + erff(x * 0.70710678118654752f)); }
 
-__device__ __forceinline__ void tmem_st_32x32(uint32_t taddr, const uint32_t (&r)[32]) {
-  asm volatile(
-      "tcgen05.st.sync.aligned.32x32b.x32.b32 [%0], "
-      "{%1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15, %16, "
-      "%17, %18, %19, %20, %21, %22, %23, %24, %25, %26, %27, %28, %29, %30, %31, %32};" ::"r"(taddr),
-      "r"(r[0]), "r"(r[1]), "r"(r[2]), "r"(r[3]), "r"(r[4]), "r"(r[5]), "r"(r[6]), "r"(r[7]), "r"(r[8]), "r"(r[9]),
-      "r"(r[10]), "r"(r[11]), "r"(r[12]), "r"(r[13]), "r"(r[14]), "r"(r[15]), "r"(r[16]), "r"(r[17]), "r"(r[18]),
-      "r"(r[19]), "r"(r[20]), "r"(r[21]), "r"(r[22]), "r"(r[23]), "r"(r[24]), "r"(r[25]), "r"(r[26]), "r"(r[27]),
-      "r"(r[28]), "r"(r[29]), "r"(r[30]), "r"(r[31])
-      : "memory");
-}
-__device__ __forceinline__ void tmem_st_wait() { asm volatile("tcgen05.wait::st.sync.aligned;" ::: "memory"); }
-
 template <int CG, int TF32, int BN>
 struct GemmCfg {
   static constexpr int BM = 128;                 // rows per CTA (UMMA M = BM * CG)
@@ -182,6 +169,13 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
       const int m = m_blk * C::BM * CG + (int)rank * C::BM + q * 32 + lane;
       const int n0 = n_blk * BN;
       const bool row_ok = m < g.M;
+      // qkv of a windowed block: token (b,y,x) is stored at its place in the 14x14-window partition of the 64x64
+      // grid (SA/modeling/image_encoder.py:243-264), so the attention kernel reads whole windows with one TMA box
+      int mo = m;
+      if (g.win_remap) {
+        const int b = m >> 12, y = (m >> 6) & 63, x = m & 63;
+        mo = (b * 25 + (y / 14) * 5 + x / 14) * 196 + (y % 14) * 14 + x % 14;
+      }
       mbar_wait(tfull_bar(as), aphase);
       tc_fence_after();
       const uint32_t taddr = tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)(as * BN);
@@ -211,7 +205,7 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
             }
             if constexpr (EPI == EPI_BIAS_BF16 || EPI == EPI_BIAS_GELU_BF16) {
               if (row_ok) {
-                __nv_bfloat16* o = reinterpret_cast<__nv_bfloat16*>(g.out) + (size_t)m * g.ldo + col;
+                __nv_bfloat16* o = reinterpret_cast<__nv_bfloat16*>(g.out) + (size_t)mo * g.ldo + col;
 #pragma unroll
                 for (int h = 0; h < 2; ++h) {
                   uint32_t pk[8];
@@ -254,7 +248,7 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
           tmem_ld_32x32(taddr + c * 32, v);
           tmem_ld_wait();
           if constexpr (EPI == EPI_RESID_LN_F32) {
-            const int mm = row_ok ? m : 0;
+            const int mm = row_ok ? (g.resid_mod ? m % g.resid_mod : m) : 0;
             const float* r = g.resid + (size_t)mm * g.ldo + c * 32;
 #pragma unroll
             for (int h = 0; h < 4; ++h) {
