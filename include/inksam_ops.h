@@ -39,7 +39,28 @@ enum {
 int inksam_op_gemm(int cg, int tf32, int bn, int epi, const void* A, int lda, const void* W, int ldw, int M, int N,
                    int K, void* out, int ldo, const float* bias, const float* resid, const float* rowadd,
                    int rowadd_mod, const float* ln_w, const float* ln_b, float ln_eps, const float* hyper,
-                   int a_conv3x3, int conv_c, void* stream);
+                   int a_conv3x3, int conv_c, int win_remap, int resid_mod, void* stream);
+
+/* Encoder attention for B images: softmax(q k^T * hd^-0.5 + decomposed rel-pos bias) v, all heads
+ * (SA/modeling/image_encoder.py:224-240,325-361).  windowed == 0: qkv is bf16 [B*4096][3*D] in token order and rel is
+ * the bf16 table [256][hd] (rows 0..126 rel_pos_h, 128..254 rel_pos_w).  windowed == 1: qkv is bf16 [B*25*196][3*D] in
+ * 14x14-window order with the qkv bias in the rows of padded tokens, rel is [64][hd] (rows 0..26 / 32..58).
+ * out: bf16 [B*4096][D] in token order. */
+int inksam_op_attention(int windowed, const void* qkv, const void* rel, void* out, int B, int heads, int head_dim, void* stream);
+
+/* nn.LayerNorm over the last dim (fp32 in, bf16 out); plain != 0 only casts. image_encoder.py:168,180. */
+int inksam_op_layernorm(const float* x, const float* w, const float* b, void* out, int M, int D, float eps, int plain, void* stream);
+
+/* Sam.preprocess + PatchEmbed im2col: out bf16 [B*4096][768]. hw is a HOST array. modeling/sam.py:164-174. */
+int inksam_op_patchify(const void* images, int dtype, int B, const int* hw, long long img_stride, long long row_pitch,
+                       long long plane_stride, const float* mean, const float* stdv, void* out, void* stream);
+
+/* qkv bias into the padded-token rows of a window-ordered qkv matrix. image_encoder.py:258-259. */
+int inksam_op_fill_pad_rows(void* qkv, const float* bias, int B, int cols, void* stream);
+
+/* Sam.postprocess_masks + threshold, fused. modeling/sam.py:133-162, predictor.py:238-241. */
+int inksam_op_postprocess(const float* low, unsigned char* masks, float* logits, int K, int in_h, int in_w, int H, int W,
+                          float thr, void* stream);
 
 const char* inksam_last_error(void);
 

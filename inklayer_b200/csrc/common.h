@@ -32,4 +32,16 @@ int make_tmap_bf16_box(CUtensorMap* out, const void* base, uint64_t rows, uint64
 int launch_gemm(int cg, int tf32, int bn, int epi, const void* A, int lda, const void* W, int ldw, GemmArgs g,
                 int num_sms, cudaStream_t st);
 
+int launch_attention(int windowed, const void* qkv, const void* rel, void* out, int B, int heads, int head_dim,
+                     cudaStream_t st);
+int launch_patchify(const void* images, int dtype, int B, const int* hw, long long img_stride, long long row_pitch,
+                    long long plane_stride, const float* mean, const float* stdv, void* out, cudaStream_t st);
+int launch_layernorm_bf16(const float* x, const float* w, const float* b, void* out, int M, int D, float eps, int plain,
+                          cudaStream_t st);
+int launch_fill_pad_rows(void* qkv, const float* bias, int B, int cols, cudaStream_t st);
+int launch_repack(const float* in, void* out, int out_bf16, const long long* ishape, int ndim, const int* perm,
+                  cudaStream_t st);
+int launch_postprocess(const float* low, unsigned char* masks, float* logits, int K, int in_h, int in_w, int H, int W,
+                       float thr, cudaStream_t st);
+
 }  // namespace inksam

@@ -1,0 +1,606 @@
+// Host engine behind include/inksam.h: weight store + repack, workspace, and the kernel sequences of
+// inksam_encode (image encoder) and inksam_decode_boxes (prompt encoder + mask decoder + post-process).
+#include "common.h"
+#include "decoder_ops.h"
+#include "inksam.h"
+
+#include <cstring>
+#include <string>
+#include <unordered_map>
+#include <vector>
+
+using namespace inksam;
+
+namespace {
+
+struct Tensor {
+  void* p = nullptr;
+  long long n = 0;
+  bool bf16 = false;
+  std::vector<long long> shape;
+};
+
+struct BlockW {
+  const float *n1_w, *n1_b, *n2_w, *n2_b, *qkv_b, *proj_b, *lin1_b, *lin2_b;
+  const void *qkv_w, *proj_w, *lin1_w, *lin2_w;
+  void* rel;  // bf16 rel-pos table [256][hd] (global) or [64][hd] (windowed)
+  bool global;
+};
+
+}  // namespace
+
+struct inksam_handle {
+  inksam_config cfg{};
+  int device = 0, num_sms = 148, head_dim = 0;
+  bool finalized = false;
+  long long launches = 0;
+  std::unordered_map<std::string, Tensor> w;
+  std::vector<void*> owned;  // derived device buffers
+  std::vector<BlockW> blocks;
+  // decoder derived
+  DecWeights dec{};
+  float *pe = nullptr;                       // dense PE, token-major [4096][256]
+  float *wkvq[2] = {nullptr, nullptr}, *bkvq[2] = {nullptr, nullptr}, *ra[2] = {nullptr, nullptr};  // [384][256], [384], [4096][384]
+  float *wkvf = nullptr, *bkvf = nullptr, *raf = nullptr;                                            // [256][256], [256], [4096][256]
+  // workspaces (grow-only)
+  void* enc_ws = nullptr; size_t enc_ws_bytes = 0;
+  void* dec_ws = nullptr; size_t dec_ws_bytes = 0;
+};
+
+namespace {
+
+bool ends_with(const std::string& s, const char* suf) {
+  const size_t n = strlen(suf);
+  return s.size() >= n && s.compare(s.size() - n, n, suf) == 0;
+}
+bool starts_with(const std::string& s, const char* pre) { return s.rfind(pre, 0) == 0; }
+
+int dev_alloc(inksam_handle* h, void** p, size_t bytes) {
+  CUDA_TRY(cudaMalloc(p, bytes));
+  h->owned.push_back(*p);
+  return 0;
+}
+
+int grow(void** p, size_t* have, size_t need) {
+  if (need <= *have) return 0;
+  if (*p) { CUDA_TRY(cudaDeviceSynchronize()); CUDA_TRY(cudaFree(*p)); *p = nullptr; *have = 0; }
+  CUDA_TRY(cudaMalloc(p, need));
+  *have = need;
+  return 0;
+}
+
+const Tensor* find(const inksam_handle* h, const std::string& key) {
+  auto it = h->w.find(key);
+  return it == h->w.end() ? nullptr : &it->second;
+}
+
+int need_f32(const inksam_handle* h, const std::string& key, const float** out) {
+  const Tensor* t = find(h, key);
+  if (!t) return set_error("finalize: tensor '%s' was never loaded", key.c_str());
+  *out = static_cast<const float*>(t->p);
+  return 0;
+}
+int need_any(const inksam_handle* h, const std::string& key, const void** out) {
+  const Tensor* t = find(h, key);
+  if (!t) return set_error("finalize: tensor '%s' was never loaded", key.c_str());
+  *out = t->p;
+  return 0;
+}
+
+// tcgen05 GEMM wrapper: out = epilogue(A * W^T)
+struct G {
+  int tf32 = 0, bn = 256, epi = 0;
+  const void* A = nullptr; int lda = 0;
+  const void* W = nullptr; int ldw = 0;
+  GemmArgs g{};
+};
+int run_gemm(inksam_handle* h, const G& c, cudaStream_t st) {
+  ++h->launches;
+  return launch_gemm(1, c.tf32, c.bn, c.epi, c.A, c.lda, c.W, c.ldw, c.g, h->num_sms, st);
+}
+
+}  // namespace
+
+extern "C" {
+
+int inksam_create(const inksam_config* cfg, int device, inksam_handle** out) {
+  if (!cfg || !out) return set_error("inksam_create: null argument");
+  if (cfg->img_size != 1024 || cfg->patch_size != 16 || cfg->window_size != 14 || cfg->out_chans != 256)
+    return set_error("inksam_create: only img_size 1024 / patch 16 / window 14 / out_chans 256 are built (got %d/%d/%d/%d)",
+                     cfg->img_size, cfg->patch_size, cfg->window_size, cfg->out_chans);
+  if (cfg->num_heads < 1 || cfg->embed_dim % cfg->num_heads != 0)
+    return set_error("inksam_create: embed_dim %d not divisible by num_heads %d", cfg->embed_dim, cfg->num_heads);
+  const int hd = cfg->embed_dim / cfg->num_heads;
+  if (hd != 64 && hd != 80) return set_error("inksam_create: head_dim %d not supported (64 or 80)", hd);
+  if (cfg->embed_dim % 32 != 0 || cfg->embed_dim > 1280) return set_error("inksam_create: embed_dim %d unsupported", cfg->embed_dim);
+  if (cfg->num_global < 0 || cfg->num_global > 8) return set_error("inksam_create: num_global %d not in 0..8", cfg->num_global);
+  int ndev = 0;
+  CUDA_TRY(cudaGetDeviceCount(&ndev));
+  if (device < 0 || device >= ndev) return set_error("inksam_create: device %d not present (%d CUDA devices)", device, ndev);
+  CUDA_TRY(cudaSetDevice(device));
+  cudaDeviceProp prop;
+  CUDA_TRY(cudaGetDeviceProperties(&prop, device));
+  if (prop.major != 10)
+    return set_error("inksam_create: device %d is sm_%d%d; this library contains sm_100a code only", device, prop.major, prop.minor);
+  auto* h = new inksam_handle();
+  h->cfg = *cfg;
+  h->device = device;
+  h->num_sms = prop.multiProcessorCount;
+  h->head_dim = hd;
+  *out = h;
+  return 0;
+}
+
+void inksam_destroy(inksam_handle* h) {
+  if (!h) return;
+  cudaSetDevice(h->device);
+  cudaDeviceSynchronize();
+  for (auto& kv : h->w) cudaFree(kv.second.p);
+  for (void* p : h->owned) cudaFree(p);
+  if (h->enc_ws) cudaFree(h->enc_ws);
+  if (h->dec_ws) cudaFree(h->dec_ws);
+  delete h;
+}
+
+long long inksam_launch_count(const inksam_handle* h) { return h ? h->launches : 0; }
+
+int inksam_load_tensor(inksam_handle* h, const char* key_c, const float* data, const int64_t* shape, int ndim, void* stream) {
+  if (!h || !key_c || !data || !shape) return set_error("inksam_load_tensor: null argument");
+  if (ndim < 1 || ndim > 4) return set_error("inksam_load_tensor: '%s' has %d dims (1..4 supported)", key_c, ndim);
+  auto st = static_cast<cudaStream_t>(stream);
+  CUDA_TRY(cudaSetDevice(h->device));
+  const std::string key(key_c);
+  if (!(starts_with(key, "image_encoder.") || starts_with(key, "prompt_encoder.") || starts_with(key, "mask_decoder.")))
+    return set_error("inksam_load_tensor: unknown key '%s'", key_c);
+  if (starts_with(key, "prompt_encoder.mask_downscaling.") || key == "prompt_encoder.not_a_point_embed.weight" ||
+      key == "prompt_encoder.point_embeddings.0.weight" || key == "prompt_encoder.point_embeddings.1.weight")
+    return 0;  // not on the box-prompt path
+  long long ishape[4], n = 1;
+  for (int d = 0; d < ndim; ++d) { ishape[d] = shape[d]; n *= shape[d]; }
+
+  bool to_bf16 = false;
+  const int* perm = nullptr;
+  static const int perm_0231[4] = {0, 2, 3, 1}, perm_2310[4] = {2, 3, 1, 0};
+  if (starts_with(key, "image_encoder.") && ends_with(key, ".weight") && ndim >= 2 &&
+      (ends_with(key, "attn.qkv.weight") || ends_with(key, "attn.proj.weight") || ends_with(key, "mlp.lin1.weight") ||
+       ends_with(key, "mlp.lin2.weight") || key == "image_encoder.patch_embed.proj.weight" ||
+       key == "image_encoder.neck.0.weight" || key == "image_encoder.neck.2.weight"))
+    to_bf16 = true;
+  if (key == "image_encoder.neck.2.weight") perm = perm_0231;  // [o][c][ky][kx] -> [o][ky][kx][c]
+  if (key == "mask_decoder.output_upscaling.0.weight" || key == "mask_decoder.output_upscaling.3.weight")
+    perm = perm_2310;  // ConvTranspose2d [c][o][dy][dx] -> [dy][dx][o][c]: rows (dy,dx,o) of a [4*O][C] GEMM weight
+  if (perm && ndim != 4) return set_error("inksam_load_tensor: '%s' must be 4-D", key_c);
+
+  Tensor t;
+  t.n = n; t.bf16 = to_bf16;
+  t.shape.assign(ishape, ishape + ndim);
+  auto it = h->w.find(key);
+  if (it != h->w.end()) { cudaFree(it->second.p); h->w.erase(it); }
+  CUDA_TRY(cudaMalloc(&t.p, (size_t)n * (to_bf16 ? 2 : 4)));
+  ++h->launches;
+  if (launch_repack(data, t.p, to_bf16 ? 1 : 0, ishape, ndim, perm, st)) { cudaFree(t.p); return -1; }
+  h->w.emplace(key, std::move(t));
+  h->finalized = false;
+  return 0;
+}
+
+}  // extern "C"
+
+// ================================================================================================ finalize
+namespace {
+
+int build_rel_table(inksam_handle* h, const std::string& pre, bool global, void** out, cudaStream_t st) {
+  const int side = global ? 64 : 14, rows = global ? 256 : 64, hd = h->head_dim;
+  const Tensor* rh = find(h, pre + "rel_pos_h");
+  const Tensor* rw = find(h, pre + "rel_pos_w");
+  if (!rh || !rw) return set_error("finalize: '%srel_pos_h/w' missing", pre.c_str());
+  for (const Tensor* t : {rh, rw})
+    if (t->shape.size() != 2 || t->shape[0] != 2 * side - 1 || t->shape[1] != hd)
+      return set_error("finalize: '%srel_pos_*' has shape [%lld,%lld], expected [%d,%d] (the interpolating branch of "
+                       "get_rel_pos is not built)", pre.c_str(), t->shape[0], t->shape.size() > 1 ? t->shape[1] : 0LL,
+                       2 * side - 1, hd);
+  INK_TRY(dev_alloc(h, out, (size_t)rows * hd * 2));
+  CUDA_TRY(cudaMemsetAsync(*out, 0, (size_t)rows * hd * 2, st));
+  const long long shp[2] = {2 * side - 1, hd};
+  h->launches += 2;
+  INK_TRY(launch_repack(static_cast<const float*>(rh->p), *out, 1, shp, 2, nullptr, st));
+  INK_TRY(launch_repack(static_cast<const float*>(rw->p), static_cast<__nv_bfloat16*>(*out) + (size_t)(rows / 2) * hd, 1, shp, 2,
+                        nullptr, st));
+  return 0;
+}
+
+// rows [r0, r0+rows) of dst (row length cols floats) <- src
+int copy_rows(float* dst, int r0, const float* src, int rows, int cols, cudaStream_t st) {
+  CUDA_TRY(cudaMemcpyAsync(dst + (size_t)r0 * cols, src, (size_t)rows * cols * 4, cudaMemcpyDeviceToDevice, st));
+  return 0;
+}
+
+int finalize_decoder(inksam_handle* h, cudaStream_t st) {
+  DecWeights& d = h->dec;
+  const std::string M = "mask_decoder.", T = "mask_decoder.transformer.", P = "prompt_encoder.";
+  INK_TRY(need_f32(h, M + "iou_token.weight", &d.iou_token));
+  INK_TRY(need_f32(h, M + "mask_tokens.weight", &d.mask_tokens));
+  INK_TRY(need_f32(h, P + "pe_layer.positional_encoding_gaussian_matrix", &d.gauss));
+  INK_TRY(need_f32(h, P + "point_embeddings.2.weight", &d.corner0));
+  INK_TRY(need_f32(h, P + "point_embeddings.3.weight", &d.corner1));
+  auto lin = [&](const std::string& k, const float** w, const float** b) -> int {
+    INK_TRY(need_f32(h, k + ".weight", w));
+    return need_f32(h, k + ".bias", b);
+  };
+  for (int l = 0; l < 2; ++l) {
+    DecLayerW& L = d.layer[l];
+    const std::string p = T + "layers." + std::to_string(l) + ".";
+    INK_TRY(lin(p + "self_attn.q_proj", &L.sa_q_w, &L.sa_q_b));
+    INK_TRY(lin(p + "self_attn.k_proj", &L.sa_k_w, &L.sa_k_b));
+    INK_TRY(lin(p + "self_attn.v_proj", &L.sa_v_w, &L.sa_v_b));
+    INK_TRY(lin(p + "self_attn.out_proj", &L.sa_o_w, &L.sa_o_b));
+    INK_TRY(lin(p + "norm1", &L.n1_w, &L.n1_b));
+    INK_TRY(lin(p + "cross_attn_token_to_image.q_proj", &L.t2i_q_w, &L.t2i_q_b));
+    INK_TRY(lin(p + "cross_attn_token_to_image.out_proj", &L.t2i_o_w, &L.t2i_o_b));
+    INK_TRY(lin(p + "norm2", &L.n2_w, &L.n2_b));
+    INK_TRY(lin(p + "mlp.lin1", &L.mlp1_w, &L.mlp1_b));
+    INK_TRY(lin(p + "mlp.lin2", &L.mlp2_w, &L.mlp2_b));
+    INK_TRY(lin(p + "norm3", &L.n3_w, &L.n3_b));
+    INK_TRY(lin(p + "cross_attn_image_to_token.k_proj", &L.i2t_k_w, &L.i2t_k_b));
+    INK_TRY(lin(p + "cross_attn_image_to_token.v_proj", &L.i2t_v_w, &L.i2t_v_b));
+  }
+  INK_TRY(lin(T + "final_attn_token_to_image.q_proj", &d.fin_q_w, &d.fin_q_b));
+  INK_TRY(lin(T + "final_attn_token_to_image.out_proj", &d.fin_o_w, &d.fin_o_b));
+  INK_TRY(lin(T + "norm_final_attn", &d.nf_w, &d.nf_b));
+  for (int i = 0; i < 3; ++i) {
+    INK_TRY(lin(M + "output_hypernetworks_mlps.0.layers." + std::to_string(i), &d.hyp_w[i], &d.hyp_b[i]));
+    INK_TRY(lin(M + "iou_prediction_head.layers." + std::to_string(i), &d.iou_w[i], &d.iou_b[i]));
+  }
+
+  // dense positional encoding of the 64x64 grid (depends on the weights only)
+  INK_TRY(dev_alloc(h, reinterpret_cast<void**>(&h->pe), (size_t)4096 * 256 * 4));
+  ++h->launches;
+  INK_TRY(launch_dense_pe(d.gauss, h->pe, st));
+
+  // Image-side projections merged per transformer layer: rows [0,128) k of token->image, [128,256) v of
+  // token->image, [256,384) q of image->token (all read the same keys, transformer.py:164-180).  k and q take
+  // keys + key_pe: the PE part is box- and image-independent, so pe * W^T is precomputed as a row-add table.
+  float* wra = nullptr;  // [384][256]: Wk ; 0 ; Wq  (weights that multiply the PE)
+  INK_TRY(dev_alloc(h, reinterpret_cast<void**>(&wra), (size_t)384 * 256 * 4));
+  for (int l = 0; l < 3; ++l) {
+    const bool fin = (l == 2);
+    const int N = fin ? 256 : 384;
+    const std::string t2i = fin ? T + "final_attn_token_to_image." : T + "layers." + std::to_string(l) + ".cross_attn_token_to_image.";
+    const std::string i2t = T + "layers." + std::to_string(l) + ".cross_attn_image_to_token.";
+    float *wm = nullptr, *bm = nullptr, *ra = nullptr;
+    INK_TRY(dev_alloc(h, reinterpret_cast<void**>(&wm), (size_t)N * 256 * 4));
+    INK_TRY(dev_alloc(h, reinterpret_cast<void**>(&bm), (size_t)N * 4));
+    INK_TRY(dev_alloc(h, reinterpret_cast<void**>(&ra), (size_t)4096 * N * 4));
+    const float *kw, *kb, *vw, *vb, *qw = nullptr, *qb = nullptr;
+    INK_TRY(lin(t2i + "k_proj", &kw, &kb));
+    INK_TRY(lin(t2i + "v_proj", &vw, &vb));
+    if (!fin) INK_TRY(lin(i2t + "q_proj", &qw, &qb));
+    CUDA_TRY(cudaMemsetAsync(wra, 0, (size_t)384 * 256 * 4, st));
+    INK_TRY(copy_rows(wm, 0, kw, 128, 256, st));
+    INK_TRY(copy_rows(wm, 128, vw, 128, 256, st));
+    INK_TRY(copy_rows(bm, 0, kb, 1, 128, st));
+    INK_TRY(copy_rows(bm + 128, 0, vb, 1, 128, st));
+    INK_TRY(copy_rows(wra, 0, kw, 128, 256, st));
+    if (!fin) {
+      INK_TRY(copy_rows(wm, 256, qw, 128, 256, st));
+      INK_TRY(copy_rows(bm + 256, 0, qb, 1, 128, st));
+      INK_TRY(copy_rows(wra, 256, qw, 128, 256, st));
+    }
+    G c;
+    c.tf32 = 1; c.bn = 128; c.epi = EPI_BIAS_F32;
+    c.A = h->pe; c.lda = 256; c.W = wra; c.ldw = 256;
+    c.g.M = 4096; c.g.N = N; c.g.K = 256; c.g.ldo = N; c.g.out = ra;
+    INK_TRY(run_gemm(h, c, st));
+    if (fin) { h->wkvf = wm; h->bkvf = bm; h->raf = ra; }
+    else { h->wkvq[l] = wm; h->bkvq[l] = bm; h->ra[l] = ra; }
+  }
+  return 0;
+}
+
+}  // namespace
+
+extern "C" int inksam_finalize_weights(inksam_handle* h, void* stream) {
+  if (!h) return set_error("inksam_finalize_weights: null handle");
+  auto st = static_cast<cudaStream_t>(stream);
+  CUDA_TRY(cudaSetDevice(h->device));
+  for (void* p : h->owned) cudaFree(p);
+  h->owned.clear();
+  h->blocks.clear();
+  const int D = h->cfg.embed_dim;
+  const Tensor* qkv0 = find(h, "image_encoder.blocks.0.attn.qkv.weight");
+  if (!qkv0 || qkv0->shape.size() != 2 || qkv0->shape[0] != 3 * D || qkv0->shape[1] != D)
+    return set_error("finalize: image_encoder.blocks.0.attn.qkv.weight missing or not [%d,%d]", 3 * D, D);
+  for (int i = 0; i < h->cfg.depth; ++i) {
+    const std::string p = "image_encoder.blocks." + std::to_string(i) + ".";
+    BlockW b{};
+    b.global = false;
+    for (int g = 0; g < h->cfg.num_global; ++g) b.global |= (h->cfg.global_attn_indexes[g] == i);
+    INK_TRY(need_f32(h, p + "norm1.weight", &b.n1_w));
+    INK_TRY(need_f32(h, p + "norm1.bias", &b.n1_b));
+    INK_TRY(need_f32(h, p + "norm2.weight", &b.n2_w));
+    INK_TRY(need_f32(h, p + "norm2.bias", &b.n2_b));
+    INK_TRY(need_any(h, p + "attn.qkv.weight", &b.qkv_w));
+    INK_TRY(need_f32(h, p + "attn.qkv.bias", &b.qkv_b));
+    INK_TRY(need_any(h, p + "attn.proj.weight", &b.proj_w));
+    INK_TRY(need_f32(h, p + "attn.proj.bias", &b.proj_b));
+    INK_TRY(need_any(h, p + "mlp.lin1.weight", &b.lin1_w));
+    INK_TRY(need_f32(h, p + "mlp.lin1.bias", &b.lin1_b));
+    INK_TRY(need_any(h, p + "mlp.lin2.weight", &b.lin2_w));
+    INK_TRY(need_f32(h, p + "mlp.lin2.bias", &b.lin2_b));
+    INK_TRY(build_rel_table(h, p + "attn.", b.global, &b.rel, st));
+    h->blocks.push_back(b);
+  }
+  for (const char* k : {"image_encoder.pos_embed", "image_encoder.patch_embed.proj.weight", "image_encoder.patch_embed.proj.bias",
+                        "image_encoder.neck.0.weight", "image_encoder.neck.1.weight", "image_encoder.neck.1.bias",
+                        "image_encoder.neck.2.weight", "image_encoder.neck.3.weight", "image_encoder.neck.3.bias",
+                        "prompt_encoder.no_mask_embed.weight", "mask_decoder.output_upscaling.0.weight",
+                        "mask_decoder.output_upscaling.0.bias", "mask_decoder.output_upscaling.1.weight",
+                        "mask_decoder.output_upscaling.1.bias", "mask_decoder.output_upscaling.3.weight",
+                        "mask_decoder.output_upscaling.3.bias"})
+    if (!find(h, k)) return set_error("finalize: tensor '%s' was never loaded", k);
+  for (int l = 0; l < 2; ++l)
+    for (const char* s : {"cross_attn_image_to_token.out_proj.weight", "cross_attn_image_to_token.out_proj.bias", "norm4.weight",
+                          "norm4.bias"})
+      if (!find(h, "mask_decoder.transformer.layers." + std::to_string(l) + "." + s))
+        return set_error("finalize: tensor 'mask_decoder.transformer.layers.%d.%s' was never loaded", l, s);
+  INK_TRY(finalize_decoder(h, st));
+  h->finalized = true;
+  return 0;
+}
+
+// ================================================================================================ encode
+namespace {
+
+size_t align_up(size_t x) { return (x + 1023) & ~size_t(1023); }
+
+int encode_chunk(inksam_handle* h, const void* images, int dtype, int B, const int* hw, long long img_stride,
+                 long long row_pitch, long long plane_stride, float* emb_out, cudaStream_t st) {
+  const int D = h->cfg.embed_dim, heads = h->cfg.num_heads, hd = h->head_dim;
+  const int M = B * 4096;
+  const size_t WROWS = (size_t)B * 25 * 196;  // window-ordered rows (>= M)
+  // workspace carve-up
+  const size_t sz_x = align_up((size_t)M * D * 4), sz_xn = align_up((size_t)M * D * 2);
+  const size_t sz_qkv = align_up(WROWS * 3 * D * 2), sz_attn = sz_xn, sz_h = align_up((size_t)M * 4 * D * 2);
+  const size_t sz_pad = align_up((size_t)B * 66 * 66 * 256 * 2);
+  const size_t sz_patch = align_up((size_t)M * 768 * 2);
+  const size_t sz_hp = sz_h > sz_patch ? sz_h : sz_patch;  // patches alias the MLP hidden buffer
+  INK_TRY(grow(&h->enc_ws, &h->enc_ws_bytes, sz_x + sz_xn + sz_qkv + sz_attn + sz_hp + sz_pad));
+  char* base = static_cast<char*>(h->enc_ws);
+  float* x = reinterpret_cast<float*>(base);
+  void* xn = base + sz_x;
+  void* qkv = base + sz_x + sz_xn;
+  void* attn = base + sz_x + sz_xn + sz_qkv;
+  void* hbuf = base + sz_x + sz_xn + sz_qkv + sz_attn;
+  void* pad = base + sz_x + sz_xn + sz_qkv + sz_attn + sz_hp;
+
+  const float *pos, *patch_b, *n1w, *n1b, *n3w, *n3b;
+  const void *patch_w, *neck0, *neck2;
+  INK_TRY(need_f32(h, "image_encoder.pos_embed", &pos));
+  INK_TRY(need_any(h, "image_encoder.patch_embed.proj.weight", &patch_w));
+  INK_TRY(need_f32(h, "image_encoder.patch_embed.proj.bias", &patch_b));
+  INK_TRY(need_any(h, "image_encoder.neck.0.weight", &neck0));
+  INK_TRY(need_f32(h, "image_encoder.neck.1.weight", &n1w));
+  INK_TRY(need_f32(h, "image_encoder.neck.1.bias", &n1b));
+  INK_TRY(need_any(h, "image_encoder.neck.2.weight", &neck2));
+  INK_TRY(need_f32(h, "image_encoder.neck.3.weight", &n3w));
+  INK_TRY(need_f32(h, "image_encoder.neck.3.bias", &n3b));
+
+  // K1: normalise + patch gather, then the patch-embed GEMM with bias + pos_embed -> fp32 residual stream
+  ++h->launches;
+  INK_TRY(launch_patchify(images, dtype, B, hw, img_stride, row_pitch, plane_stride, h->cfg.pixel_mean, h->cfg.pixel_std, hbuf, st));
+  {
+    G c; c.epi = EPI_BIAS_ROWADD_F32; c.A = hbuf; c.lda = 768; c.W = patch_w; c.ldw = 768;
+    c.g.M = M; c.g.N = D; c.g.K = 768; c.g.ldo = D; c.g.out = x; c.g.bias = patch_b; c.g.rowadd = pos; c.g.rowadd_mod = 4096;
+    INK_TRY(run_gemm(h, c, st));
+  }
+  for (const BlockW& b : h->blocks) {
+    ++h->launches;
+    INK_TRY(launch_layernorm_bf16(x, b.n1_w, b.n1_b, xn, M, D, 1e-6f, 0, st));
+    {
+      G c; c.epi = EPI_BIAS_BF16; c.A = xn; c.lda = D; c.W = b.qkv_w; c.ldw = D;
+      c.g.M = M; c.g.N = 3 * D; c.g.K = D; c.g.ldo = 3 * D; c.g.out = qkv; c.g.bias = b.qkv_b; c.g.win_remap = b.global ? 0 : 1;
+      INK_TRY(run_gemm(h, c, st));
+    }
+    if (!b.global) {
+      ++h->launches;
+      INK_TRY(launch_fill_pad_rows(qkv, b.qkv_b, B, 3 * D, st));
+    }
+    ++h->launches;
+    INK_TRY(launch_attention(b.global ? 0 : 1, qkv, b.rel, attn, B, heads, hd, st));
+    {
+      G c; c.epi = EPI_BIAS_RESID_F32; c.A = attn; c.lda = D; c.W = b.proj_w; c.ldw = D;
+      c.g.M = M; c.g.N = D; c.g.K = D; c.g.ldo = D; c.g.out = x; c.g.bias = b.proj_b; c.g.resid = x;
+      INK_TRY(run_gemm(h, c, st));
+    }
+    ++h->launches;
+    INK_TRY(launch_layernorm_bf16(x, b.n2_w, b.n2_b, xn, M, D, 1e-6f, 0, st));
+    {
+      G c; c.epi = EPI_BIAS_GELU_BF16; c.A = xn; c.lda = D; c.W = b.lin1_w; c.ldw = D;
+      c.g.M = M; c.g.N = 4 * D; c.g.K = D; c.g.ldo = 4 * D; c.g.out = hbuf; c.g.bias = b.lin1_b;
+      INK_TRY(run_gemm(h, c, st));
+    }
+    {
+      G c; c.epi = EPI_BIAS_RESID_F32; c.A = hbuf; c.lda = 4 * D; c.W = b.lin2_w; c.ldw = 4 * D;
+      c.g.M = M; c.g.N = D; c.g.K = 4 * D; c.g.ldo = D; c.g.out = x; c.g.bias = b.lin2_b; c.g.resid = x;
+      INK_TRY(run_gemm(h, c, st));
+    }
+  }
+  // neck: 1x1 conv + LayerNorm2d -> zero-bordered bf16 map; 3x3 conv (implicit GEMM over 9 taps) + LayerNorm2d -> NCHW fp32
+  ++h->launches;
+  INK_TRY(launch_layernorm_bf16(x, nullptr, nullptr, xn, M, D, 0.f, 1, st));
+  CUDA_TRY(cudaMemsetAsync(pad, 0, (size_t)B * 66 * 66 * 256 * 2, st));
+  {
+    G c; c.epi = EPI_LN_BF16_PAD; c.A = xn; c.lda = D; c.W = neck0; c.ldw = D;
+    c.g.M = M; c.g.N = 256; c.g.K = D; c.g.ldo = 256; c.g.out = pad; c.g.ln_w = n1w; c.g.ln_b = n1b; c.g.ln_eps = 1e-6f;
+    INK_TRY(run_gemm(h, c, st));
+  }
+  {
+    G c; c.epi = EPI_LN_F32_NCHW; c.A = pad; c.lda = 256; c.W = neck2; c.ldw = 9 * 256;
+    c.g.M = M; c.g.N = 256; c.g.K = 9 * 256; c.g.ldo = 256; c.g.out = emb_out; c.g.ln_w = n3w; c.g.ln_b = n3b; c.g.ln_eps = 1e-6f;
+    c.g.a_conv3x3 = 1; c.g.conv_c = 256;
+    INK_TRY(run_gemm(h, c, st));
+  }
+  return 0;
+}
+
+}  // namespace
+
+extern "C" int inksam_encode(inksam_handle* h, const void* images, int dtype, int B, const int* hw, int64_t img_stride,
+                             int64_t row_pitch, int64_t plane_stride, float* embeddings_out, void* stream) {
+  if (!h || !images || !hw || !embeddings_out) return set_error("inksam_encode: null argument");
+  if (!h->finalized) return set_error("inksam_encode: weights not finalized (call inksam_finalize_weights)");
+  if (B < 1) return set_error("inksam_encode: batch %d", B);
+  if (dtype != INKSAM_IMAGE_U8_HWC && dtype != INKSAM_IMAGE_F32_CHW) return set_error("inksam_encode: dtype %d", dtype);
+  CUDA_TRY(cudaSetDevice(h->device));
+  auto st = static_cast<cudaStream_t>(stream);
+  for (int b0 = 0; b0 < B; b0 += 32) {  // patchify takes at most 32 images per launch
+    const int nb = B - b0 < 32 ? B - b0 : 32;
+    INK_TRY(encode_chunk(h, static_cast<const char*>(images) + (long long)b0 * img_stride, dtype, nb, hw + 2 * b0, img_stride,
+                         row_pitch, plane_stride, embeddings_out + (size_t)b0 * 256 * 4096, st));
+  }
+  return 0;
+}
+
+// ================================================================================================ decode
+namespace {
+
+constexpr int kBoxChunk = 64;  // boxes decoded per pass (bounds the workspace at ~1.1 GB)
+
+int decode_chunk(inksam_handle* h, const float* keys0, const float* kvq0, char* ws, const float* boxes, int n, int in_h,
+                 int in_w, int H, int W, uint8_t* masks, float* iou, float* low, float* logits, float thr, cudaStream_t st) {
+  const std::string T = "mask_decoder.transformer.layers.";
+  // per-chunk buffers
+  size_t off = 0;
+  auto take = [&](size_t bytes) { char* p = ws + off; off += align_up(bytes); return p; };
+  float* keysb = reinterpret_cast<float*>(take((size_t)n * 4096 * 256 * 4));
+  float* kvq = reinterpret_cast<float*>(take((size_t)n * 4096 * 384 * 4));   // also holds the 128x128x64 upscaled map
+  float* a1 = reinterpret_cast<float*>(take((size_t)n * 4096 * 128 * 4));
+  DecState s{};
+  s.boxes = boxes;
+  s.queries = reinterpret_cast<float*>(take((size_t)n * 7 * 256 * 4));
+  s.query_pe = reinterpret_cast<float*>(take((size_t)n * 7 * 256 * 4));
+  s.q_t2i = reinterpret_cast<float*>(take((size_t)n * 7 * 128 * 4));
+  s.attn_t2i = reinterpret_cast<float*>(take((size_t)n * 7 * 128 * 4));
+  s.kv_i2t = reinterpret_cast<float*>(take((size_t)n * 2 * 7 * 128 * 4));
+  s.hyper = reinterpret_cast<float*>(take((size_t)n * 32 * 4));
+  s.iou = iou;
+  const int Mb = n * 4096;
+
+  auto tokens = [&](int phase, int layer) { ++h->launches; return launch_decoder_tokens(h->dec, s, n, phase, layer, st); };
+  auto t2i = [&](const float* kv, long long stride, int ld) {
+    ++h->launches;
+    return launch_decoder_t2i(s.q_t2i, kv, stride, ld, s.attn_t2i, n, st);
+  };
+  auto i2t = [&](const float* q, long long stride) {
+    ++h->launches;
+    return launch_decoder_i2t(q, stride, 384, 256, s.kv_i2t, a1, n, st);
+  };
+  // keys <- norm4(keys + out_proj(image->token attention))   (transformer.py:176-180)
+  auto keys_update = [&](int layer, const float* resid, int resid_mod) -> int {
+    const float *ow, *ob, *nw, *nb;
+    INK_TRY(need_f32(h, T + std::to_string(layer) + ".cross_attn_image_to_token.out_proj.weight", &ow));
+    INK_TRY(need_f32(h, T + std::to_string(layer) + ".cross_attn_image_to_token.out_proj.bias", &ob));
+    INK_TRY(need_f32(h, T + std::to_string(layer) + ".norm4.weight", &nw));
+    INK_TRY(need_f32(h, T + std::to_string(layer) + ".norm4.bias", &nb));
+    G c; c.tf32 = 1; c.epi = EPI_RESID_LN_F32; c.A = a1; c.lda = 128; c.W = ow; c.ldw = 128;
+    c.g.M = Mb; c.g.N = 256; c.g.K = 128; c.g.ldo = 256; c.g.out = keysb; c.g.bias = ob; c.g.resid = resid;
+    c.g.resid_mod = resid_mod; c.g.ln_w = nw; c.g.ln_b = nb; c.g.ln_eps = 1e-5f;
+    return run_gemm(h, c, st);
+  };
+
+  // ---- layer 0: the image-side k / v / q are shared by all boxes (kvq0)
+  INK_TRY(tokens(0, 0));
+  INK_TRY(t2i(kvq0, 0, 384));
+  INK_TRY(tokens(2, 0));
+  INK_TRY(i2t(kvq0, 0));
+  INK_TRY(keys_update(0, keys0, 4096));
+  // ---- layer 1: per-box keys
+  {
+    G c; c.tf32 = 1; c.bn = 128; c.epi = EPI_BIAS_ROWADD_F32; c.A = keysb; c.lda = 256; c.W = h->wkvq[1]; c.ldw = 256;
+    c.g.M = Mb; c.g.N = 384; c.g.K = 256; c.g.ldo = 384; c.g.out = kvq; c.g.bias = h->bkvq[1]; c.g.rowadd = h->ra[1];
+    c.g.rowadd_mod = 4096;
+    INK_TRY(run_gemm(h, c, st));
+  }
+  INK_TRY(tokens(1, 1));
+  INK_TRY(t2i(kvq, 4096LL * 384, 384));
+  INK_TRY(tokens(2, 1));
+  INK_TRY(i2t(kvq, 4096LL * 384));
+  INK_TRY(keys_update(1, keysb, 0));
+  // ---- final token -> image attention
+  {
+    G c; c.tf32 = 1; c.epi = EPI_BIAS_ROWADD_F32; c.A = keysb; c.lda = 256; c.W = h->wkvf; c.ldw = 256;
+    c.g.M = Mb; c.g.N = 256; c.g.K = 256; c.g.ldo = 256; c.g.out = kvq; c.g.bias = h->bkvf; c.g.rowadd = h->raf;
+    c.g.rowadd_mod = 4096;
+    INK_TRY(run_gemm(h, c, st));
+  }
+  INK_TRY(tokens(3, 0));
+  INK_TRY(t2i(kvq, 4096LL * 256, 256));
+  INK_TRY(tokens(4, 0));
+  // ---- upscaling: ConvT(256->64,k2,s2)+LayerNorm2d+GELU, ConvT(64->32,k2,s2)+GELU, dot with the hypernetwork vector
+  const float *u0w, *u0b, *u1w, *u1b, *u3w, *u3b;
+  INK_TRY(need_f32(h, "mask_decoder.output_upscaling.0.weight", &u0w));
+  INK_TRY(need_f32(h, "mask_decoder.output_upscaling.0.bias", &u0b));
+  INK_TRY(need_f32(h, "mask_decoder.output_upscaling.1.weight", &u1w));
+  INK_TRY(need_f32(h, "mask_decoder.output_upscaling.1.bias", &u1b));
+  INK_TRY(need_f32(h, "mask_decoder.output_upscaling.3.weight", &u3w));
+  INK_TRY(need_f32(h, "mask_decoder.output_upscaling.3.bias", &u3b));
+  float* up1 = kvq;  // [n][128][128][64]
+  {
+    G c; c.tf32 = 1; c.epi = EPI_UPSCALE1; c.A = keysb; c.lda = 256; c.W = u0w; c.ldw = 256;
+    c.g.M = Mb; c.g.N = 256; c.g.K = 256; c.g.ldo = 256; c.g.out = up1; c.g.bias = u0b; c.g.ln_w = u1w; c.g.ln_b = u1b;
+    c.g.ln_eps = 1e-6f;
+    INK_TRY(run_gemm(h, c, st));
+  }
+  {
+    G c; c.tf32 = 1; c.bn = 128; c.epi = EPI_UPSCALE2_MASK; c.A = up1; c.lda = 64; c.W = u3w; c.ldw = 64;
+    c.g.M = n * 16384; c.g.N = 128; c.g.K = 64; c.g.ldo = 128; c.g.out = low; c.g.bias = u3b; c.g.hyper = s.hyper;
+    INK_TRY(run_gemm(h, c, st));
+  }
+  // ---- fused upsample + crop + resize + threshold
+  ++h->launches;
+  INK_TRY(launch_postprocess(low, masks, logits, n, in_h, in_w, H, W, thr, st));
+  return 0;
+}
+
+}  // namespace
+
+extern "C" int inksam_decode_boxes(inksam_handle* h, const float* embedding, const float* boxes, int K, int in_h, int in_w,
+                                   int orig_h, int orig_w, uint8_t* masks_out, float* iou_out, float* lowres_out,
+                                   float* logits_out, float mask_threshold, void* stream) {
+  if (!h || !embedding || !iou_out || !lowres_out) return set_error("inksam_decode_boxes: null argument");
+  if (!h->finalized) return set_error("inksam_decode_boxes: weights not finalized (call inksam_finalize_weights)");
+  if (K < 0) return set_error("inksam_decode_boxes: K=%d", K);
+  if (K == 0) return 0;
+  if (!boxes) return set_error("inksam_decode_boxes: null boxes");
+  if (in_h < 1 || in_w < 1 || in_h > 1024 || in_w > 1024 || orig_h < 1 || orig_w < 1)
+    return set_error("inksam_decode_boxes: bad sizes input %dx%d original %dx%d", in_h, in_w, orig_h, orig_w);
+  CUDA_TRY(cudaSetDevice(h->device));
+  auto st = static_cast<cudaStream_t>(stream);
+  const int nc = K < kBoxChunk ? K : kBoxChunk;
+  const size_t shared_bytes = align_up((size_t)4096 * 256 * 4) + align_up((size_t)4096 * 384 * 4);
+  const size_t chunk_bytes = align_up((size_t)nc * 4096 * 256 * 4) + align_up((size_t)nc * 4096 * 384 * 4) +
+                             align_up((size_t)nc * 4096 * 128 * 4) + 8 * align_up((size_t)nc * 7 * 256 * 4);
+  INK_TRY(grow(&h->dec_ws, &h->dec_ws_bytes, shared_bytes + chunk_bytes));
+  char* ws = static_cast<char*>(h->dec_ws);
+  float* keys0 = reinterpret_cast<float*>(ws);
+  float* kvq0 = reinterpret_cast<float*>(ws + align_up((size_t)4096 * 256 * 4));
+  const float* nomask;
+  INK_TRY(need_f32(h, "prompt_encoder.no_mask_embed.weight", &nomask));
+  // keys of layer 0 = embedding + dense no-mask prompt, token-major; their k / v / q projections once per image
+  ++h->launches;
+  INK_TRY(launch_decoder_keys0(embedding, nomask, keys0, st));
+  {
+    G c; c.tf32 = 1; c.bn = 128; c.epi = EPI_BIAS_ROWADD_F32; c.A = keys0; c.lda = 256; c.W = h->wkvq[0]; c.ldw = 256;
+    c.g.M = 4096; c.g.N = 384; c.g.K = 256; c.g.ldo = 384; c.g.out = kvq0; c.g.bias = h->bkvq[0]; c.g.rowadd = h->ra[0];
+    c.g.rowadd_mod = 4096;
+    INK_TRY(run_gemm(h, c, st));
+  }
+  const size_t HW = (size_t)orig_h * orig_w;
+  for (int k0 = 0; k0 < K; k0 += kBoxChunk) {
+    const int n = K - k0 < kBoxChunk ? K - k0 : kBoxChunk;
+    INK_TRY(decode_chunk(h, keys0, kvq0, ws + shared_bytes, boxes + 4 * k0, n, in_h, in_w, orig_h, orig_w,
+                         masks_out ? masks_out + k0 * HW : nullptr, iou_out + k0, lowres_out + (size_t)k0 * 65536,
+                         logits_out ? logits_out + k0 * HW : nullptr, mask_threshold, st));
+  }
+  return 0;
+}

@@ -1,0 +1,221 @@
+"""`Sam` model object and the `build_sam*` factories of the drop-in surface (segment_anything/build_sam.py:14-107,
+segment_anything/modeling/sam.py:18-47).  The object owns a libinksam handle instead of nn.Modules; PyTorch is used
+for tensor ownership, streams and host<->device copies only.  Every compute call goes through the C ABI in
+include/inksam.h and raises if the CUDA library or a B200 is missing -- there is no CPU path."""
+from __future__ import annotations
+
+import ctypes
+from types import SimpleNamespace
+from typing import Dict, Optional, Sequence, Tuple
+
+import torch
+
+from . import _lib
+from .config import CONFIGS, SamConfig, config_from_state_dict
+from .weights import state_dict_shapes, synthetic_state_dict
+
+
+def _stream(device: torch.device) -> ctypes.c_void_p:
+    return ctypes.c_void_p(torch.cuda.current_stream(device).cuda_stream)
+
+
+def _ptr(t: Optional[torch.Tensor]) -> ctypes.c_void_p:
+    return ctypes.c_void_p(0 if t is None else t.data_ptr())
+
+
+class Sam:
+    """Stands where `segment_anything.modeling.Sam` stands for SamPredictor: `.device`, `.image_format`,
+    `.mask_threshold`, `.image_encoder.img_size`, `.to()`, `.eval()`, `.load_state_dict()`."""
+
+    mask_threshold: float = 0.0  # modeling/sam.py:19
+    image_format: str = "RGB"    # modeling/sam.py:20
+
+    def __init__(self, cfg: SamConfig) -> None:
+        self.cfg = cfg
+        self.image_encoder = SimpleNamespace(img_size=cfg.img_size)
+        self.device = torch.device("cpu")
+        self._sd: Optional[Dict[str, torch.Tensor]] = None
+        self._handle: Optional[ctypes.c_void_p] = None
+
+    # ------------------------------------------------------------------ weights
+    def load_state_dict(self, state_dict: Dict[str, torch.Tensor], strict: bool = True) -> None:
+        """Accepts the reference's flat state_dict (build_sam.py:103-106): same keys, fp32."""
+        want = {k: tuple(s) for k, s, _ in state_dict_shapes(self.cfg)}
+        missing = [k for k in want if k not in state_dict]
+        unexpected = [k for k in state_dict if k not in want]
+        if strict and (missing or unexpected):
+            raise RuntimeError(f"Error(s) in loading state_dict for Sam: missing {missing[:5]}, unexpected {unexpected[:5]}")
+        for k, shape in want.items():
+            if k in state_dict and tuple(state_dict[k].shape) != shape:
+                raise RuntimeError(f"size mismatch for {k}: checkpoint {tuple(state_dict[k].shape)}, model {shape}")
+        self._sd = {k: v.detach() for k, v in state_dict.items() if k in want}
+        if self._handle is not None:
+            self._upload()
+
+    def state_dict(self) -> Dict[str, torch.Tensor]:
+        if self._sd is None:
+            raise RuntimeError("no weights loaded")
+        return dict(self._sd)
+
+    def eval(self) -> "Sam":
+        return self
+
+    def to(self, device) -> "Sam":
+        device = torch.device(device)
+        if device.type != "cuda":
+            raise RuntimeError("inklayer_b200.Sam runs on a CUDA device only (sm_100a kernels, no CPU fallback)")
+        if device.index is None:
+            device = torch.device("cuda", torch.cuda.current_device())
+        if self._handle is not None and device == self.device:
+            return self
+        self._destroy()
+        lib = _lib.load()
+        c = _lib.InksamConfig()
+        c.embed_dim, c.depth, c.num_heads = self.cfg.embed_dim, self.cfg.depth, self.cfg.num_heads
+        c.num_global = len(self.cfg.global_attn_indexes)
+        for i, g in enumerate(self.cfg.global_attn_indexes):
+            c.global_attn_indexes[i] = g
+        c.window_size, c.img_size, c.patch_size, c.out_chans = (self.cfg.window_size, self.cfg.img_size,
+                                                                 self.cfg.patch_size, self.cfg.out_chans)
+        for i in range(3):
+            c.pixel_mean[i], c.pixel_std[i] = self.cfg.pixel_mean[i], self.cfg.pixel_std[i]
+        h = ctypes.c_void_p()
+        _lib.check(lib.inksam_create(ctypes.byref(c), device.index, ctypes.byref(h)))
+        self._handle, self.device = h, device
+        if self._sd is not None:
+            self._upload()
+        return self
+
+    def cuda(self, index: Optional[int] = None) -> "Sam":
+        return self.to(torch.device("cuda", torch.cuda.current_device() if index is None else index))
+
+    def _upload(self) -> None:
+        lib = _lib.load()
+        with torch.cuda.device(self.device):
+            st = _stream(self.device)
+            for key, t in self._sd.items():
+                d = t.to(device=self.device, dtype=torch.float32).contiguous()
+                shape = (ctypes.c_int64 * d.dim())(*d.shape)
+                _lib.check(lib.inksam_load_tensor(self._handle, key.encode(), _ptr(d), shape, d.dim(), st))
+            _lib.check(lib.inksam_finalize_weights(self._handle, st))
+            torch.cuda.current_stream(self.device).synchronize()
+
+    def _destroy(self) -> None:
+        if self._handle is not None:
+            _lib.load().inksam_destroy(self._handle)
+            self._handle = None
+
+    def __del__(self) -> None:
+        try:
+            self._destroy()
+        except Exception:
+            pass
+
+    def _require(self) -> ctypes.c_void_p:
+        if self._handle is None or self._sd is None:
+            raise RuntimeError("Sam is not on a CUDA device or has no weights: call build_sam(...).to('cuda')")
+        return self._handle
+
+    @property
+    def launch_count(self) -> int:
+        return int(_lib.load().inksam_launch_count(self._require()))
+
+    # ------------------------------------------------------------------ compute (C ABI)
+    @torch.no_grad()
+    def encode(self, images: torch.Tensor, sizes: Optional[Sequence[Tuple[int, int]]] = None) -> torch.Tensor:
+        """Sam.preprocess + image encoder (modeling/sam.py:164-174, image_encoder.py:106-116) for a batch.
+        images: uint8 [B,h,w,3] (HWC) or float32 [B,3,h,w] (values 0..255) on this device, long side <= 1024;
+        `sizes` optionally gives each image's valid (h, w) inside the container.  Returns float32 [B,256,64,64]."""
+        h = self._require()
+        if images.device != self.device:
+            raise RuntimeError(f"images are on {images.device}, model on {self.device}")
+        images = images.contiguous()
+        B = images.shape[0]
+        if images.dtype == torch.uint8 and images.dim() == 4 and images.shape[3] == 3:
+            dtype, hh, ww = 0, images.shape[1], images.shape[2]
+            row_pitch, plane = ww * 3, 0
+            img_stride = hh * ww * 3
+        elif images.dtype == torch.float32 and images.dim() == 4 and images.shape[1] == 3:
+            dtype, hh, ww = 1, images.shape[2], images.shape[3]
+            row_pitch, plane = ww * 4, hh * ww * 4
+            img_stride = 3 * hh * ww * 4
+        else:
+            raise RuntimeError(f"encode expects uint8 [B,h,w,3] or float32 [B,3,h,w], got {images.dtype} {tuple(images.shape)}")
+        if max(hh, ww) > self.cfg.img_size:
+            raise RuntimeError(f"image {hh}x{ww} exceeds img_size {self.cfg.img_size}")
+        hw = (ctypes.c_int * (2 * B))()
+        for i in range(B):
+            sh, sw = (hh, ww) if sizes is None else sizes[i]
+            hw[2 * i], hw[2 * i + 1] = int(sh), int(sw)
+        out = torch.empty((B, self.cfg.out_chans, 64, 64), dtype=torch.float32, device=self.device)
+        with torch.cuda.device(self.device):
+            _lib.check(_lib.load().inksam_encode(h, _ptr(images), dtype, B, hw, img_stride, row_pitch, plane, _ptr(out),
+                                                 _stream(self.device)))
+        return out
+
+    @torch.no_grad()
+    def decode_boxes(self, embedding: torch.Tensor, boxes: torch.Tensor, input_size: Tuple[int, int],
+                     original_size: Tuple[int, int], return_logits: bool = False):
+        """prompt encoder + mask decoder + postprocess_masks + threshold for K boxes of one image
+        (predictor.py:222-241).  embedding: float32 [1,256,64,64] or [256,64,64]; boxes: [K,4] xyxy, input frame.
+        Returns (masks bool|float [K,1,H,W], iou [K,1], low_res [K,1,256,256])."""
+        h = self._require()
+        K = int(boxes.shape[0])
+        H, W = int(original_size[0]), int(original_size[1])
+        dev = self.device
+        emb = embedding.reshape(-1, 64, 64).to(device=dev, dtype=torch.float32).contiguous()
+        bx = boxes.to(device=dev, dtype=torch.float32).contiguous()
+        iou = torch.empty((K, 1), dtype=torch.float32, device=dev)
+        low = torch.empty((K, 1, 256, 256), dtype=torch.float32, device=dev)
+        masks = None if return_logits else torch.empty((K, 1, H, W), dtype=torch.uint8, device=dev)
+        logits = torch.empty((K, 1, H, W), dtype=torch.float32, device=dev) if return_logits else None
+        if K > 0:
+            with torch.cuda.device(dev):
+                _lib.check(_lib.load().inksam_decode_boxes(
+                    h, _ptr(emb), _ptr(bx), K, int(input_size[0]), int(input_size[1]), H, W, _ptr(masks), _ptr(iou),
+                    _ptr(low), _ptr(logits), ctypes.c_float(self.mask_threshold), _stream(dev)))
+        return (logits if return_logits else masks.view(torch.bool)), iou, low
+
+
+# ---------------------------------------------------------------------------------------- factories
+def _build(name: str, checkpoint: Optional[str]) -> Sam:
+    cfg = CONFIGS[name]
+    sam = Sam(cfg)
+    if checkpoint is not None:
+        with open(checkpoint, "rb") as f:
+            sd = torch.load(f, map_location="cpu")
+        sam.load_state_dict(sd)
+    else:
+        # The reference returns torch's default random init here; there are no nn.Modules to initialise in this
+        # implementation, so checkpoint=None gives the seeded synthetic state_dict (weights.py) instead.
+        sam.load_state_dict(synthetic_state_dict(cfg, 0))
+    return sam
+
+
+def build_sam_vit_h(checkpoint: Optional[str] = None) -> Sam:
+    return _build("vit_h", checkpoint)
+
+
+def build_sam_vit_l(checkpoint: Optional[str] = None) -> Sam:
+    return _build("vit_l", checkpoint)
+
+
+def build_sam_vit_b(checkpoint: Optional[str] = None) -> Sam:
+    return _build("vit_b", checkpoint)
+
+
+build_sam = build_sam_vit_h
+
+sam_model_registry = {
+    "default": build_sam_vit_h,
+    "vit_h": build_sam_vit_h,
+    "vit_l": build_sam_vit_l,
+    "vit_b": build_sam_vit_b,
+}
+
+
+def build_sam_from_state_dict(state_dict: Dict[str, torch.Tensor], cfg: Optional[SamConfig] = None) -> Sam:
+    """Any encoder shape the kernels support (head_dim 64 or 80), inferred from the tensors when cfg is None."""
+    sam = Sam(cfg or config_from_state_dict(state_dict))
+    sam.load_state_dict(state_dict)
+    return sam

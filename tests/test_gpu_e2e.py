@@ -1,0 +1,117 @@
+"""-m gpu: the drop-in surface end to end.  SamPredictor.set_image / predict_torch on the B200 path against
+  (1) the committed golden vectors produced by the unmodified reference (tests/golden/make_golden.py), and
+  (2) the CPU oracle run here on the same weights and inputs (small configs only).
+Stated tolerances (BASELINE.md, bf16 operands vs fp32): embeddings rel-RMS <= 1e-2, low-res mask logits rel-RMS <= 1e-2,
+binarised masks IoU >= 0.99 per box."""
+import numpy as np
+import pytest
+import torch
+
+from conftest import golden_case_inputs, load_golden, mask_iou
+from gpu_util import rel_rms
+from inklayer_b200 import CONFIGS, SamPredictor, build_sam_from_state_dict
+from inklayer_b200.weights import synthetic_state_dict
+from oracle import sam_oracle as O
+
+pytestmark = pytest.mark.gpu
+
+
+def run_case(case):
+    cfg_name, seed, img, boxes = golden_case_inputs(case)
+    sd = synthetic_state_dict(CONFIGS[cfg_name], seed)
+    sam = build_sam_from_state_dict(sd, CONFIGS[cfg_name]).to("cuda")
+    pred = SamPredictor(sam)
+    pred.set_image(img)
+    tb = pred.transform.apply_boxes_torch(torch.from_numpy(boxes), img.shape[:2]).to("cuda")
+    masks, iou, low = pred.predict_torch(None, None, boxes=tb, multimask_output=False)
+    torch.cuda.synchronize()
+    return cfg_name, sd, img, boxes, pred, masks, iou, low
+
+
+@pytest.mark.parametrize("case", ["tiny_1024", "tiny80_600x750", "vit_b_750_bunny", "vit_h_1024"])
+def test_predictor_matches_reference_golden(case):
+    gold = load_golden(case)
+    cfg_name, sd, img, boxes, pred, masks, iou, low = run_case(case)
+    assert masks.dtype == torch.bool and tuple(masks.shape) == (len(boxes), 1) + img.shape[:2]
+    assert tuple(iou.shape) == (len(boxes), 1) and tuple(low.shape) == (len(boxes), 1, 256, 256)
+    emb = pred.get_image_embedding()[0].cpu().numpy()
+    e_rms = rel_rms(torch.from_numpy(emb[:, ::4, ::4].copy()), torch.from_numpy(gold["emb_sub"]))
+    l_rms = rel_rms(low.cpu()[:, :, ::4, ::4], torch.from_numpy(gold["low_sub"]))
+    ref_masks = np.unpackbits(gold["mask_bits"])[: int(np.prod(gold["mask_shape"]))].reshape(gold["mask_shape"])
+    ious = mask_iou(masks[:4].cpu().numpy(), ref_masks)
+    print(f"{case}: emb rel-RMS {e_rms:.2e}  low-res rel-RMS {l_rms:.2e}  min IoU {ious.min():.4f}  "
+          f"iou-head max err {np.abs(iou.cpu().numpy() - gold['iou']).max():.2e}")
+    assert e_rms <= 1e-2
+    assert l_rms <= 1e-2
+    assert ious.min() >= 0.99
+    assert np.abs(iou.cpu().numpy() - gold["iou"]).max() < 2e-2
+
+
+@pytest.mark.parametrize("case", ["tiny_1024", "tiny80_600x750"])
+def test_predictor_matches_oracle_full_tensors(case):
+    cfg_name, sd, img, boxes, pred, masks, iou, low = run_case(case)
+    ora = O.OraclePredictor(O.CONFIGS[cfg_name], sd)
+    ora.set_image(img)
+    tb = O.apply_boxes(torch.from_numpy(boxes), img.shape[:2])
+    m_ref, i_ref, l_ref = ora.predict_torch(tb)
+    assert rel_rms(pred.features.cpu(), ora.features) <= 1e-2
+    assert rel_rms(low.cpu(), l_ref) <= 1e-2
+    assert mask_iou(masks.cpu().numpy(), m_ref.numpy()).min() >= 0.99
+    logits, _, _ = pred.predict_torch(None, None, boxes=tb.cuda(), multimask_output=False, return_logits=True)
+    full_ref = O.postprocess_masks(O.CONFIGS[cfg_name], l_ref, ora.input_size, ora.original_size)
+    assert rel_rms(logits.cpu(), full_ref) <= 1e-2
+
+
+def test_decoder_alone_matches_oracle_on_same_embedding():
+    """Mask decoder + post-process in isolation: fp32 embedding from the oracle in, so only the decoder's own
+    tf32 / fp32 arithmetic differs.  Also covers K > one chunk (64) and ragged K."""
+    cfg_name = "vit_tiny"
+    cfg, sd = CONFIGS[cfg_name], synthetic_state_dict(CONFIGS[cfg_name], 0)
+    from inklayer_b200.synth import synthetic_boxes, synthetic_sketch
+
+    img = synthetic_sketch(0)
+    ora = O.OraclePredictor(O.CONFIGS[cfg_name], sd)
+    ora.set_image(img)
+    sam = build_sam_from_state_dict(sd, cfg).to("cuda")
+    boxes = torch.from_numpy(synthetic_boxes(7, 70))
+    m_ref, i_ref, l_ref = ora.predict_torch(boxes)
+    masks, iou, low = sam.decode_boxes(ora.features.cuda(), boxes.cuda(), (1024, 1024), (1024, 1024))
+    assert rel_rms(low.cpu(), l_ref) <= 3e-3
+    assert (iou.cpu() - i_ref).abs().max().item() < 5e-3
+    assert mask_iou(masks.cpu().numpy(), m_ref.numpy()).min() >= 0.995
+    # box independence: decoding a subset gives the same answer
+    m1, i1, l1 = sam.decode_boxes(ora.features.cuda(), boxes[5:6].cuda(), (1024, 1024), (1024, 1024))
+    assert torch.allclose(l1, low[5:6], atol=1e-5)
+
+
+def test_surface_errors_and_edge_cases():
+    cfg = CONFIGS["vit_tiny"]
+    sam = build_sam_from_state_dict(synthetic_state_dict(cfg, 0), cfg).to("cuda")
+    pred = SamPredictor(sam)
+    with pytest.raises(RuntimeError):  # predictor.py:213-214
+        pred.predict_torch(None, None, boxes=torch.zeros(1, 4, device="cuda"), multimask_output=False)
+    with pytest.raises(AssertionError):  # predictor.py:48-51
+        pred.set_image(np.zeros((64, 64, 3), np.uint8), image_format="HSV")
+    with pytest.raises(AssertionError):  # predictor.py:79-83
+        pred.set_torch_image(torch.zeros(1, 3, 512, 512, device="cuda"), (512, 512))
+    pred.set_image(np.full((300, 200, 3), 255, np.uint8))
+    assert pred.input_size == (1024, 683) and pred.original_size == (300, 200)
+    with pytest.raises(NotImplementedError):
+        pred.predict_torch(torch.zeros(1, 1, 2), torch.zeros(1, 1), multimask_output=False)
+    m, i, l = pred.predict_torch(None, None, boxes=torch.zeros(0, 4, device="cuda"), multimask_output=False)
+    assert tuple(m.shape) == (0, 1, 300, 200) and tuple(i.shape) == (0, 1) and tuple(l.shape) == (0, 1, 256, 256)
+    m, i, l = pred.predict_torch(None, None, boxes=torch.tensor([[10., 20., 500., 900.]], device="cuda"), multimask_output=False)
+    assert tuple(m.shape) == (1, 1, 300, 200) and torch.isfinite(l).all()
+    # BGR flips channels exactly like the reference (predictor.py:52-53)
+    rng = np.random.default_rng(0)
+    im = rng.integers(0, 256, (128, 128, 3), dtype=np.uint8)
+    pred.set_image(im, "BGR"); a = pred.features.clone()
+    pred.set_image(np.ascontiguousarray(im[..., ::-1]), "RGB")
+    assert torch.equal(a, pred.features)
+    # set_torch_image (float CHW) agrees with set_image (uint8 HWC) on the same pixels
+    big = rng.integers(0, 256, (1024, 768, 3), dtype=np.uint8)
+    pred.set_image(big); a = pred.features.clone()
+    pred.set_torch_image(torch.from_numpy(big).permute(2, 0, 1)[None].cuda(), (1024, 768))
+    assert torch.equal(a, pred.features)
+    pred.reset_image()
+    assert not pred.is_image_set and pred.features is None

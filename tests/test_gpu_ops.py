@@ -1,0 +1,99 @@
+"""-m gpu: the HBM-bound helper kernels against the CPU oracle / plain torch fp32, through the C ABI."""
+import ctypes
+
+import numpy as np
+import pytest
+import torch
+
+from gpu_util import ptr, rel_err, stream
+from inklayer_b200 import _lib
+from oracle import sam_oracle as O
+
+pytestmark = pytest.mark.gpu
+CFG = O.CONFIGS["vit_tiny"]
+
+
+@pytest.mark.parametrize("M,D", [(4096 + 3, 1280), (515, 160), (1000, 128), (64, 768)])
+def test_layernorm_matches_torch(M, D):
+    lib = _lib.load()
+    g = torch.Generator().manual_seed(M + D)
+    x = (torch.randn(M, D, generator=g) * 3 + 0.5).cuda()
+    w = (1 + 0.1 * torch.randn(D, generator=g)).cuda()
+    b = (0.1 * torch.randn(D, generator=g)).cuda()
+    out = torch.empty(M, D, dtype=torch.bfloat16, device="cuda")
+    _lib.check(lib.inksam_op_layernorm(ptr(x), ptr(w), ptr(b), ptr(out), M, D, ctypes.c_float(1e-6), 0, stream()))
+    ref = torch.nn.functional.layer_norm(x, (D,), w, b, 1e-6)
+    assert rel_err(out, ref) < 6e-3  # one bf16 rounding
+    _lib.check(lib.inksam_op_layernorm(ptr(x), None, None, ptr(out), M, D, ctypes.c_float(0), 1, stream()))
+    assert torch.equal(out, x.to(torch.bfloat16))
+
+
+@pytest.mark.parametrize("h,w,dtype", [(1024, 1024, 0), (819, 1024, 0), (1024, 683, 1)])
+def test_patchify_matches_preprocess(h, w, dtype):
+    """Sam.preprocess + PatchEmbed unfold (oracle.preprocess / oracle.patch_embed column order)."""
+    lib = _lib.load()
+    rng = np.random.default_rng(h * 7 + w)
+    B = 2
+    img = rng.integers(0, 256, (B, h, w, 3), dtype=np.uint8)
+    chw = torch.from_numpy(img).permute(0, 3, 1, 2).contiguous()
+    x = O.preprocess(CFG, chw)  # [B,3,1024,1024]
+    ref = x.reshape(B, 3, 64, 16, 64, 16).permute(0, 2, 4, 1, 3, 5).reshape(B * 4096, 768)
+    if dtype == 0:
+        dev = torch.from_numpy(img).cuda()
+        strides = (h * w * 3, w * 3, 0)
+    else:
+        dev = chw.float().cuda()
+        strides = (3 * h * w * 4, w * 4, h * w * 4)
+    hw = (ctypes.c_int * (2 * B))(*([h, w] * B))
+    mean = (ctypes.c_float * 3)(*CFG.pixel_mean)
+    std = (ctypes.c_float * 3)(*CFG.pixel_std)
+    out = torch.empty(B * 4096, 768, dtype=torch.bfloat16, device="cuda")
+    _lib.check(lib.inksam_op_patchify(ptr(dev), dtype, B, hw, strides[0], strides[1], strides[2], mean, std, ptr(out), stream()))
+    got = out.float().cpu()
+    assert (got - ref).abs().max().item() < 0.012  # |x| <= 2.7, bf16 rounding
+    pad = ref == 0
+    assert torch.equal(got[pad], torch.zeros_like(got[pad]))  # padding is exactly zero (normalise THEN pad)
+
+
+def test_fill_pad_rows():
+    lib = _lib.load()
+    B, cols = 2, 480
+    q = torch.full((B * 25 * 196, cols), 7.0, dtype=torch.bfloat16, device="cuda")
+    bias = torch.randn(cols, generator=torch.Generator().manual_seed(1)).cuda()
+    _lib.check(lib.inksam_op_fill_pad_rows(ptr(q), ptr(bias), B, cols, stream()))
+    q = q.float().cpu().reshape(B, 5, 5, 14, 14, cols)
+    bb = bias.to(torch.bfloat16).float().cpu()
+    n_pad = 0
+    for wy in range(5):
+        for wx in range(5):
+            for ly in range(14):
+                for lx in range(14):
+                    real = wy * 14 + ly < 64 and wx * 14 + lx < 64
+                    row = q[:, wy, wx, ly, lx]
+                    if real:
+                        assert (row == 7.0).all()
+                    else:
+                        n_pad += 1
+                        assert torch.equal(row, bb.expand_as(row))
+    assert n_pad == 4900 - 4096
+
+
+@pytest.mark.parametrize("inp,orig", [((1024, 1024), (1024, 1024)), ((819, 1024), (600, 750)), ((1024, 1024), (750, 750)),
+                                      ((1024, 577), (1333, 751))])
+def test_postprocess_matches_interpolate(inp, orig):
+    """Fused two-stage bilinear + threshold vs Sam.postprocess_masks (oracle.postprocess_masks)."""
+    lib = _lib.load()
+    K = 3
+    low = torch.randn(K, 1, 256, 256, generator=torch.Generator().manual_seed(5)) * 0.1
+    ref = O.postprocess_masks(CFG, low, inp, orig)
+    H, W = orig
+    masks = torch.empty(K, 1, H, W, dtype=torch.uint8, device="cuda")
+    logits = torch.empty(K, 1, H, W, dtype=torch.float32, device="cuda")
+    _lib.check(lib.inksam_op_postprocess(ptr(low.cuda()), ptr(masks), ptr(logits), K, inp[0], inp[1], H, W,
+                                         ctypes.c_float(0.0), stream()))
+    assert (logits.cpu() - ref).abs().max().item() < 2e-6
+    m_ref = ref > 0.0
+    disagree = (masks.cpu().bool() != m_ref)
+    assert (ref[disagree].abs() < 2e-6).all()  # only where the logit is within rounding of the threshold
+    assert disagree.float().mean().item() < 1e-4
+    assert set(masks.unique().tolist()) <= {0, 1}

@@ -23,7 +23,7 @@ def gemm(lib, cg, tf32, bn, epi, A, W, out, bias=None, resid=None, rowadd=None, 
     N, K = W.shape
     rc = lib.inksam_op_gemm(cg, tf32, bn, epi, ptr(A), A.stride(0), ptr(W), W.stride(0), M, N, K, ptr(out),
                             out.stride(0) if out.dim() == 2 else N, ptr(bias), ptr(resid), ptr(rowadd), rowadd_mod,
-                            ptr(ln_w), ptr(ln_b), ctypes.c_float(eps), ptr(None), 0, 0,
+                            ptr(ln_w), ptr(ln_b), ctypes.c_float(eps), ptr(None), 0, 0, 0, 0,
                             ctypes.c_void_p(torch.cuda.current_stream().cuda_stream))
     if rc != 0:
         raise RuntimeError(lib.inksam_last_error().decode())
