@@ -80,6 +80,12 @@ int inksam_decode_boxes(inksam_handle* h, const float* embedding, const float* b
 /* Number of kernels this handle has launched so far (bench.py's gpu_launches). */
 long long inksam_launch_count(const inksam_handle* h);
 
+/* Optional CUDA-event timing of the library's own launches, per category (bench.py's roofline figures):
+ * category 0 encoder GEMMs, 1 encoder attention, 3 decoder GEMMs (work = algorithmic FLOP), 5 mask post-process
+ * (work = algorithmic bytes); 2 and 4 are unused.  enable(1) resets; read() waits for the recorded events. */
+int inksam_profile_enable(inksam_handle* h, int on);
+int inksam_profile_read(inksam_handle* h, double* ms /*[6]*/, double* work /*[6]*/, long long* count /*[6]*/);
+
 const char* inksam_last_error(void);
 
 #ifdef __cplusplus

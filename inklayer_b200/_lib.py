@@ -32,6 +32,8 @@ SIGNATURES = {
     "inksam_decode_boxes": (c_int, [c_void_p, c_void_p, c_void_p, c_int, c_int, c_int, c_int, c_int, c_void_p, c_void_p,
                                     c_void_p, c_void_p, c_float, c_void_p]),
     "inksam_launch_count": (c_longlong, [c_void_p]),
+    "inksam_profile_enable": (c_int, [c_void_p, c_int]),
+    "inksam_profile_read": (c_int, [c_void_p, POINTER(ctypes.c_double), POINTER(ctypes.c_double), POINTER(c_longlong)]),
     "inksam_last_error": (c_char_p, []),
     "inksam_op_gemm": (c_int, [c_int, c_int, c_int, c_int, c_void_p, c_int, c_void_p, c_int, c_int, c_int, c_int, c_void_p,
                                c_int, c_void_p, c_void_p, c_void_p, c_int, c_void_p, c_void_p, c_float, c_void_p, c_int,

@@ -45,6 +45,12 @@ struct inksam_handle {
   // workspaces (grow-only)
   void* enc_ws = nullptr; size_t enc_ws_bytes = 0;
   void* dec_ws = nullptr; size_t dec_ws_bytes = 0;
+  // optional per-category CUDA-event timing of the launches (bench.py's roofline numbers)
+  bool prof_on = false;
+  int prof_cat = 0;  // category the next launches are charged to (offset by 3 inside decode)
+  struct ProfRec { int cat; double work; cudaEvent_t e0, e1; };
+  std::vector<ProfRec> prof;
+  std::vector<cudaEvent_t> ev_pool;
 };
 
 namespace {
@@ -94,8 +100,26 @@ struct G {
   const void* W = nullptr; int ldw = 0;
   GemmArgs g{};
 };
+// RAII CUDA-event bracket around one launch when profiling is enabled; `work` = algorithmic FLOPs or bytes.
+struct Prof {
+  inksam_handle* h; cudaStream_t st; size_t idx; bool on;
+  Prof(inksam_handle* h_, int cat, double work, cudaStream_t st_) : h(h_), st(st_), idx(0), on(h_->prof_on) {
+    if (!on) return;
+    cudaEvent_t e[2];
+    for (auto& x : e) {
+      if (h->ev_pool.empty()) cudaEventCreate(&x); else { x = h->ev_pool.back(); h->ev_pool.pop_back(); }
+    }
+    idx = h->prof.size();
+    h->prof.push_back({cat, work, e[0], e[1]});
+    cudaEventRecord(e[0], st);
+  }
+  ~Prof() { if (on) cudaEventRecord(h->prof[idx].e1, st); }
+};
+enum { CAT_ENC_GEMM = 0, CAT_ENC_ATTN = 1, CAT_ENC_OTHER = 2, CAT_DEC_GEMM = 3, CAT_DEC_OTHER = 4, CAT_POST = 5, CAT_N = 6 };
+
 int run_gemm(inksam_handle* h, const G& c, cudaStream_t st) {
   ++h->launches;
+  Prof p(h, h->prof_cat == 0 ? CAT_ENC_GEMM : CAT_DEC_GEMM, 2.0 * c.g.M * c.g.N * c.g.K, st);
   return launch_gemm(1, c.tf32, c.bn, c.epi, c.A, c.lda, c.W, c.ldw, c.g, h->num_sms, st);
 }
 
@@ -406,7 +430,11 @@ int encode_chunk(inksam_handle* h, const void* images, int dtype, int B, const i
       INK_TRY(launch_fill_pad_rows(qkv, b.qkv_b, B, 3 * D, st));
     }
     ++h->launches;
-    INK_TRY(launch_attention(b.global ? 0 : 1, qkv, b.rel, attn, B, heads, hd, st));
+    {
+      const double keys = b.global ? 4096.0 : 196.0, side = b.global ? 64.0 : 14.0;
+      Prof p(h, CAT_ENC_ATTN, (double)B * heads * 4096.0 * hd * (4.0 * keys + 4.0 * side), st);  // QK^T + PV + rel-pos terms
+      INK_TRY(launch_attention(b.global ? 0 : 1, qkv, b.rel, attn, B, heads, hd, st));
+    }
     {
       G c; c.epi = EPI_BIAS_RESID_F32; c.A = attn; c.lda = D; c.W = b.proj_w; c.ldw = D;
       c.g.M = M; c.g.N = D; c.g.K = D; c.g.ldo = D; c.g.out = x; c.g.bias = b.proj_b; c.g.resid = x;
@@ -558,7 +586,10 @@ int decode_chunk(inksam_handle* h, const float* keys0, const float* kvq0, char* 
   }
   // ---- fused upsample + crop + resize + threshold
   ++h->launches;
-  INK_TRY(launch_postprocess(low, masks, logits, n, in_h, in_w, H, W, thr, st));
+  {
+    Prof p(h, CAT_POST, (double)n * (65536.0 * 4 + (double)H * W * ((masks ? 1 : 0) + (logits ? 4 : 0))), st);
+    INK_TRY(launch_postprocess(low, masks, logits, n, in_h, in_w, H, W, thr, st));
+  }
   return 0;
 }
 
@@ -576,6 +607,7 @@ extern "C" int inksam_decode_boxes(inksam_handle* h, const float* embedding, con
     return set_error("inksam_decode_boxes: bad sizes input %dx%d original %dx%d", in_h, in_w, orig_h, orig_w);
   CUDA_TRY(cudaSetDevice(h->device));
   auto st = static_cast<cudaStream_t>(stream);
+  struct CatGuard { inksam_handle* h; CatGuard(inksam_handle* x) : h(x) { h->prof_cat = 1; } ~CatGuard() { h->prof_cat = 0; } } guard(h);
   const int nc = K < kBoxChunk ? K : kBoxChunk;
   const size_t shared_bytes = align_up((size_t)4096 * 256 * 4) + align_up((size_t)4096 * 384 * 4);
   const size_t chunk_bytes = align_up((size_t)nc * 4096 * 256 * 4) + align_up((size_t)nc * 4096 * 384 * 4) +
@@ -601,6 +633,29 @@ extern "C" int inksam_decode_boxes(inksam_handle* h, const float* embedding, con
     INK_TRY(decode_chunk(h, keys0, kvq0, ws + shared_bytes, boxes + 4 * k0, n, in_h, in_w, orig_h, orig_w,
                          masks_out ? masks_out + k0 * HW : nullptr, iou_out + k0, lowres_out + (size_t)k0 * 65536,
                          logits_out ? logits_out + k0 * HW : nullptr, mask_threshold, st));
+  }
+  return 0;
+}
+
+// ================================================================================================ profiling
+extern "C" int inksam_profile_enable(inksam_handle* h, int on) {
+  if (!h) return set_error("inksam_profile_enable: null handle");
+  for (auto& r : h->prof) { h->ev_pool.push_back(r.e0); h->ev_pool.push_back(r.e1); }
+  h->prof.clear();
+  h->prof_on = on != 0;
+  return 0;
+}
+
+// ms[c], work[c], count[c] for c in {0 encoder GEMM (FLOP), 1 encoder attention (FLOP), 2 unused, 3 decoder GEMM (FLOP),
+// 4 unused, 5 post-process (bytes)}: summed CUDA-event durations of the launches since inksam_profile_enable(h, 1).
+extern "C" int inksam_profile_read(inksam_handle* h, double* ms, double* work, long long* count) {
+  if (!h || !ms || !work || !count) return set_error("inksam_profile_read: null argument");
+  for (int c = 0; c < CAT_N; ++c) { ms[c] = 0; work[c] = 0; count[c] = 0; }
+  for (auto& r : h->prof) {
+    CUDA_TRY(cudaEventSynchronize(r.e1));
+    float t = 0.f;
+    CUDA_TRY(cudaEventElapsedTime(&t, r.e0, r.e1));
+    ms[r.cat] += t; work[r.cat] += r.work; count[r.cat] += 1;
   }
   return 0;
 }

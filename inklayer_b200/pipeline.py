@@ -73,7 +73,7 @@ class SketchSegmenter:
         self.d2h_bytes += off
         torch.cuda.current_stream(dev).synchronize()
         host = stage.numpy()
-        return [host[o:o + n].reshape(shape).astype(bool) for o, n, shape in views]
+        return [host[o:o + n].view(np.bool_).reshape(shape).copy() for o, n, shape in views]
 
 
 _default: Optional[SketchSegmenter] = None

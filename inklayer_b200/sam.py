@@ -120,6 +120,17 @@ class Sam:
     def launch_count(self) -> int:
         return int(_lib.load().inksam_launch_count(self._require()))
 
+    def profile(self, on: bool) -> None:
+        """Start (and reset) / stop per-category CUDA-event timing of the library's launches."""
+        _lib.check(_lib.load().inksam_profile_enable(self._require(), 1 if on else 0))
+
+    def profile_read(self):
+        """{category: (ms, work, launches)} since profile(True); waits for the recorded events."""
+        ms, work, cnt = (ctypes.c_double * 6)(), (ctypes.c_double * 6)(), (ctypes.c_longlong * 6)()
+        _lib.check(_lib.load().inksam_profile_read(self._require(), ms, work, cnt))
+        names = {0: "encoder_gemm", 1: "encoder_attention", 3: "decoder_gemm", 5: "postprocess"}
+        return {n: (ms[c], work[c], int(cnt[c])) for c, n in names.items()}
+
     # ------------------------------------------------------------------ compute (C ABI)
     @torch.no_grad()
     def encode(self, images: torch.Tensor, sizes: Optional[Sequence[Tuple[int, int]]] = None) -> torch.Tensor:
