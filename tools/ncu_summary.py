@@ -1,0 +1,73 @@
+#!/usr/bin/env python
+"""Summaries of ncu output for profiles/.
+
+    tools/ncu_summary.py launches gpurun_out/launches.csv            # per-kernel totals of a launch list
+    tools/ncu_summary.py full gpurun_out/prof_gemm.ncu-rep [...]     # key metrics of every launch in --set full reports
+"""
+import collections
+import csv
+import io
+import re
+import subprocess
+import sys
+
+KEYS = [
+    "gpu__time_duration.sum",
+    "sm__pipe_tensor_cycles_active.avg.pct_of_peak_sustained_active",
+    "sm__inst_executed_pipe_tensor_subpipe_hmma.avg.pct_of_peak_sustained_active",
+    "sm__throughput.avg.pct_of_peak_sustained_elapsed",
+    "gpu__dram_throughput.avg.pct_of_peak_sustained_elapsed",
+    "dram__bytes_read.sum",
+    "dram__bytes_write.sum",
+    "launch__registers_per_thread",
+    "launch__grid_size",
+    "launch__block_size",
+    "sm__warps_active.avg.pct_of_peak_sustained_active",
+]
+
+
+def short(name: str) -> str:
+    return re.sub(r"\(.*", "", name).replace("void ", "").replace("inksam::", "")
+
+
+def launches(path: str) -> None:
+    lines = [l for l in open(path) if l.startswith('"')]
+    r = csv.reader(lines)
+    hdr = next(r)
+    ix = {h: i for i, h in enumerate(hdr)}
+    agg = collections.defaultdict(lambda: [0, 0.0])
+    tot = 0.0
+    for row in r:
+        if len(row) < len(hdr):
+            continue
+        v = float(row[ix["Metric Value"]].replace(",", ""))
+        u = row[ix["Metric Unit"]]
+        v = v / 1e3 if u in ("ns", "nsecond") else v * 1e3 if u in ("ms", "msecond") else v
+        k = short(row[ix["Kernel Name"]])
+        agg[k][0] += 1
+        agg[k][1] += v
+        tot += v
+    print(f"# {path}: {sum(a[0] for a in agg.values())} launches, {tot / 1e3:.3f} ms total (ncu per-launch times: cold cache, serialised)")
+    print(f"{'total ms':>10} {'count':>6} {'avg us':>9} {'share':>7}  kernel")
+    for k, (n, t) in sorted(agg.items(), key=lambda kv: -kv[1][1]):
+        print(f"{t / 1e3:10.3f} {n:6d} {t / n:9.1f} {100 * t / tot:6.1f}%  {k}")
+
+
+def full(paths) -> None:
+    for p in paths:
+        out = subprocess.run(["ncu", "-i", p, "--page", "raw", "--csv"], capture_output=True, text=True).stdout
+        rows = list(csv.reader(io.StringIO(out)))
+        hdr, units = rows[0], rows[1]
+        ix = [hdr.index(k) for k in KEYS if k in hdr]
+        print(f"# {p}")
+        print(" | ".join(["kernel"] + [f"{hdr[i]} [{units[i]}]" for i in ix]))
+        for row in rows[2:]:
+            print(" | ".join([short(row[hdr.index("Kernel Name")])] + [row[i] for i in ix]))
+        print()
+
+
+if __name__ == "__main__":
+    if sys.argv[1] == "launches":
+        launches(sys.argv[2])
+    else:
+        full(sys.argv[2:])
