@@ -85,7 +85,7 @@ static int launch_one(const CUtensorMap& tA, const CUtensorMap& tB, const GemmAr
   if (tiles < clusters) clusters = tiles;
   cudaLaunchConfig_t cfg{};
   cfg.gridDim = dim3(clusters * CG);
-  cfg.blockDim = dim3(256);
+  cfg.blockDim = dim3(384);
   cfg.dynamicSmemBytes = C::SMEM_BYTES;
   cfg.stream = st;
   cudaLaunchAttribute attr[1];

@@ -7,8 +7,10 @@
 //   warp 1      MMA issuer: one thread issues tcgen05.mma (UMMA M = 128*CG, N = BN, K = 32 bytes),
 //               accumulators live in TMEM, double buffered (2 x BN columns)
 //   warp 2      TMEM allocator
-//   warps 4..7  epilogue: tcgen05.ld (thread == output row), fused bias / GELU / residual / LayerNorm,
-//               direct 32-byte vector stores
+//   warps 4..11 epilogue: tcgen05.ld (thread == output row; warp w reads TMEM lanes 32*(w%4).., the two warps of a
+//               lane quarter split the tile's columns), fused bias / GELU / residual / LayerNorm, direct 32-byte
+//               vector stores.  Residual / row-add operands are prefetched one 32-column chunk ahead so that their
+//               DRAM latency is off the critical path.  The row-wise LayerNorm epilogues use warps 4..7 only.
 //
 // This one kernel replaces every nn.Linear / 1x1 conv / 3x3 conv / conv-transpose GEMM on the hot path:
 //   reference SA/modeling/image_encoder.py:227 (qkv), :238 (proj), common.py:21-26 (MLP),
@@ -20,7 +22,29 @@
 
 namespace inksam {
 
-__device__ __forceinline__ float gelu_erf(float x) { return 0.5f * x * (1.0f + erff(x * 0.70710678118654752f)); }
+// Exact (erf-form) GELU, nn.GELU() default (SA/modeling/common.py:18, image_encoder.py:30):
+//   gelu(x) = x/2 + |x|/2 * erf(|x|/sqrt2), erf by Abramowitz-Stegun 7.1.26 (|error| <= 1.5e-7, below fp32 erff's
+// own error after the 0.5*x scaling), branch-free: 2 MUFU (rcp, ex2) + 12 FMA-pipe instructions per element.
+__device__ __forceinline__ float gelu_erf(float x) {
+  const float z = fabsf(x) * 0.70710678118654752f;
+  float t;
+  asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(t) : "f"(fmaf(0.3275911f, z, 1.0f)));
+  float p = fmaf(1.061405429f, t, -1.453152027f);
+  p = fmaf(p, t, 1.421413741f);
+  p = fmaf(p, t, -0.284496736f);
+  p = fmaf(p, t, 0.254829592f);
+  p *= t;
+  const float e = ex2_approx(z * z * -1.4426950408889634f);
+  const float erf_abs = fmaf(-p, e, 1.0f);
+  const float hx = 0.5f * x;
+  return fmaf(fabsf(hx), erf_abs, hx);
+}
+
+// epilogue warps per CTA: 8 (two per TMEM lane quarter, splitting the columns) except for the epilogues that
+// need whole-row LayerNorm statistics, which keep one warp per lane quarter
+__host__ __device__ constexpr int gemm_epi_warps(int epi) {
+  return (epi == EPI_LN_BF16_PAD || epi == EPI_LN_F32_NCHW || epi == EPI_RESID_LN_F32) ? 4 : 8;
+}
 
 template <int CG, int TF32, int BN>
 struct GemmCfg {
@@ -37,7 +61,7 @@ struct GemmCfg {
 };
 
 template <int CG, int TF32, int BN, int EPI>
-__global__ void __launch_bounds__(256, 1)
+__global__ void __launch_bounds__(384, 1)
 gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB, const GemmArgs g) {
   using C = GemmCfg<CG, TF32, BN>;
   extern __shared__ uint8_t smem_raw[];
@@ -74,7 +98,7 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
     }
     for (int s = 0; s < 2; ++s) {
       mbar_init(tfull_bar(s), 1);          // one tcgen05.commit
-      mbar_init(tempty_bar(s), 128 * CG);  // every epilogue thread of the pair
+      mbar_init(tempty_bar(s), 32 * gemm_epi_warps(EPI) * CG);  // every epilogue thread of the pair
     }
     fence_mbar_init();
   }
@@ -159,9 +183,11 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
       }
     }
     __syncwarp();
-  } else if (warp >= 4) {
+  } else if (warp >= 4 && warp < 4 + gemm_epi_warps(EPI)) {
     // ------------------------------------------------------------ epilogue (thread == output row)
     const int q = warp & 3;  // TMEM sub-partition this warp may read: lanes [32q, 32q+32)
+    constexpr int CSPLIT = gemm_epi_warps(EPI) / 4;  // warps sharing a lane quarter
+    const int half = (warp - 4) >> 2;                // which share of the columns is this warp's
     int as = 0;
     uint32_t aphase = 0;
     for (int tile = cluster_id; tile < num_tiles; tile += num_clusters) {
@@ -176,22 +202,47 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
         const int b = m >> 12, y = (m >> 6) & 63, x = m & 63;
         mo = (b * 25 + (y / 14) * 5 + x / 14) * 196 + (y % 14) * 14 + x % 14;
       }
-      mbar_wait(tfull_bar(as), aphase);
-      tc_fence_after();
       const uint32_t taddr = tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)(as * BN);
       constexpr int NCH = BN / 32;
-
-      if constexpr (EPI == EPI_BIAS_BF16 || EPI == EPI_BIAS_GELU_BF16 || EPI == EPI_BIAS_RESID_F32 ||
-                    EPI == EPI_BIAS_ROWADD_F32 || EPI == EPI_BIAS_F32) {
-        uint32_t v[2][32];
-        tmem_ld_32x32(taddr, v[0]);
+      constexpr int NCW = NCH / CSPLIT;  // 32-column chunks handled by this warp
+      const int c_first = half * NCW;
+      constexpr bool kHasAdd = (EPI == EPI_BIAS_RESID_F32 || EPI == EPI_BIAS_ROWADD_F32);
+      constexpr bool kSimple = (EPI == EPI_BIAS_BF16 || EPI == EPI_BIAS_GELU_BF16 || EPI == EPI_BIAS_RESID_F32 ||
+                                EPI == EPI_BIAS_ROWADD_F32 || EPI == EPI_BIAS_F32);
+      // residual / row-add operand of this thread's row, fetched one chunk ahead of its use (the first chunk even
+      // before the accumulator is complete).  In-place use (out == resid) is safe: a chunk is loaded before the
+      // same thread stores it, and no other thread touches it.
+      uint32_t radd[kHasAdd ? 2 : 1][32];
+      const float* add_row = nullptr;
+      if constexpr (kHasAdd) {
+        const int mm = row_ok ? m : 0;
+        if constexpr (EPI == EPI_BIAS_RESID_F32) add_row = g.resid + (size_t)mm * g.ldo + n0;
+        else add_row = g.rowadd + (size_t)(mm % g.rowadd_mod) * g.N + n0;
+        if (n0 + c_first * 32 < g.N) {
 #pragma unroll
-        for (int c = 0; c < NCH; ++c) {
+          for (int h = 0; h < 4; ++h) ld_global_v8(add_row + c_first * 32 + h * 8, *reinterpret_cast<uint32_t(*)[8]>(&radd[0][h * 8]));
+        }
+      }
+      mbar_wait(tfull_bar(as), aphase);
+      tc_fence_after();
+
+      if constexpr (kSimple) {
+        uint32_t v[32];
+        float* f = reinterpret_cast<float*>(v);
+#pragma unroll
+        for (int ci = 0; ci < NCW; ++ci) {
+          const int c = c_first + ci;
           const int col = n0 + c * 32;
-          tmem_ld_wait();
-          if (c + 1 < NCH) tmem_ld_32x32(taddr + (c + 1) * 32, v[(c + 1) & 1]);
-          if (col < g.N) {
-            float* f = reinterpret_cast<float*>(v[c & 1]);
+          if (col < g.N) {  // warp-uniform
+            tmem_ld_32x32(taddr + c * 32, v);
+            if constexpr (kHasAdd) {
+              if (ci + 1 < NCW && col + 32 < g.N) {
+#pragma unroll
+                for (int h = 0; h < 4; ++h)
+                  ld_global_v8(add_row + (c + 1) * 32 + h * 8, *reinterpret_cast<uint32_t(*)[8]>(&radd[(ci + 1) & 1][h * 8]));
+              }
+            }
+            tmem_ld_wait();
             if (g.bias != nullptr) {
 #pragma unroll
               for (int j = 0; j < 32; j += 4) {
@@ -217,19 +268,14 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
             } else {
               if (row_ok) {
                 float* o = reinterpret_cast<float*>(g.out) + (size_t)m * g.ldo + col;
-                const float* add = nullptr;
-                if constexpr (EPI == EPI_BIAS_RESID_F32) add = g.resid + (size_t)m * g.ldo + col;
-                if constexpr (EPI == EPI_BIAS_ROWADD_F32) add = g.rowadd + (size_t)(m % g.rowadd_mod) * g.N + col;
 #pragma unroll
                 for (int h = 0; h < 4; ++h) {
                   uint32_t pk[8];
-                  if constexpr (EPI != EPI_BIAS_F32) {
-                    ld_global_v8(add + h * 8, pk);
 #pragma unroll
-                    for (int j = 0; j < 8; ++j) pk[j] = __float_as_uint(__uint_as_float(pk[j]) + f[h * 8 + j]);
-                  } else {
-#pragma unroll
-                    for (int j = 0; j < 8; ++j) pk[j] = __float_as_uint(f[h * 8 + j]);
+                  for (int j = 0; j < 8; ++j) {
+                    float x = f[h * 8 + j];
+                    if constexpr (kHasAdd) x += __uint_as_float(radd[ci & 1][h * 8 + j]);
+                    pk[j] = __float_as_uint(x);
                   }
                   st_global_v8(o + h * 8, pk);
                 }
@@ -318,7 +364,8 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
         uint32_t v[2][32];
         const int bx = m >> 12, y = (m >> 6) & 63, x = m & 63;
 #pragma unroll 1
-        for (int sp = 0; sp < 4; ++sp) {
+        for (int spi = 0; spi < 2; ++spi) {
+          const int sp = half * 2 + spi;  // the two warps of a lane quarter take the sub-pixel rows dy = 0 / 1
           float* f0 = reinterpret_cast<float*>(v[0]);
           float* f1 = reinterpret_cast<float*>(v[1]);
           tmem_ld_32x32(taddr + sp * 64, v[0]);
@@ -368,20 +415,20 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
         const int mm = row_ok ? m : 0;
         const int bx = mm >> 14, Y = (mm >> 7) & 127, X = mm & 127;
         const float* hy = g.hyper + (size_t)bx * 32;
-        float logit[4];
+        float logit[2];
 #pragma unroll
-        for (int sp = 0; sp < 4; ++sp) {
+        for (int spi = 0; spi < 2; ++spi) {
+          const int sp = half * 2 + spi;  // this warp's sub-pixel row dy = half
           tmem_ld_32x32(taddr + sp * 32, v);
           tmem_ld_wait();
           float acc = 0.f;
 #pragma unroll
           for (int j = 0; j < 32; ++j) acc += gelu_erf(f[j] + __ldg(g.bias + j)) * __ldg(hy + j);
-          logit[sp] = acc;
+          logit[spi] = acc;
         }
         if (row_ok) {
-          float* o = reinterpret_cast<float*>(g.out) + ((size_t)bx * 256 + 2 * Y) * 256 + 2 * X;
+          float* o = reinterpret_cast<float*>(g.out) + ((size_t)bx * 256 + 2 * Y + half) * 256 + 2 * X;
           *reinterpret_cast<float2*>(o) = make_float2(logit[0], logit[1]);
-          *reinterpret_cast<float2*>(o + 256) = make_float2(logit[2], logit[3]);
         }
       }
 
