@@ -77,6 +77,17 @@ int inksam_decode_boxes(inksam_handle* h, const float* embedding, const float* b
                         int orig_h, int orig_w, uint8_t* masks_out, float* iou_out, float* lowres_out,
                         float* logits_out, float mask_threshold, void* stream);
 
+/* The same for the boxes of B images in ONE pass (the reference's own multi-image entry Sam.forward loops this per
+ * image, modeling/sam.py:101-130; InkLayer's `main.py --dir` loop is the caller that batches, main.py:27-32).  Boxes are
+ * grouped by image: image i owns counts[i] consecutive rows of `boxes`.  counts / in_hw / orig_hw are HOST arrays
+ * ([B], [B][2], [B][2]); every other pointer is a device pointer.
+ * embeddings: float32 [B][256][64][64];  boxes: float32 [sum counts][4], each in its own image's resized-input frame;
+ * masks_out (may be NULL) / logits_out (may be NULL): image after image, counts[i] maps of orig_hw[i] each, densely
+ * packed;  iou_out: float32 [sum counts];  lowres_out: float32 [sum counts][256][256].  1 <= B <= 64. */
+int inksam_decode_batch(inksam_handle* h, const float* embeddings, int B, const float* boxes, const int* counts,
+                        const int* in_hw, const int* orig_hw, uint8_t* masks_out, float* iou_out, float* lowres_out,
+                        float* logits_out, float mask_threshold, void* stream);
+
 /* Number of kernels this handle has launched so far (bench.py's gpu_launches). */
 long long inksam_launch_count(const inksam_handle* h);
 

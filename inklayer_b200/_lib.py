@@ -31,6 +31,8 @@ SIGNATURES = {
     "inksam_encode": (c_int, [c_void_p, c_void_p, c_int, c_int, POINTER(c_int), c_int64, c_int64, c_int64, c_void_p, c_void_p]),
     "inksam_decode_boxes": (c_int, [c_void_p, c_void_p, c_void_p, c_int, c_int, c_int, c_int, c_int, c_void_p, c_void_p,
                                     c_void_p, c_void_p, c_float, c_void_p]),
+    "inksam_decode_batch": (c_int, [c_void_p, c_void_p, c_int, c_void_p, POINTER(c_int), POINTER(c_int), POINTER(c_int),
+                                    c_void_p, c_void_p, c_void_p, c_void_p, c_float, c_void_p]),
     "inksam_launch_count": (c_longlong, [c_void_p]),
     "inksam_profile_enable": (c_int, [c_void_p, c_int]),
     "inksam_profile_read": (c_int, [c_void_p, POINTER(ctypes.c_double), POINTER(ctypes.c_double), POINTER(c_longlong)]),

@@ -255,8 +255,10 @@ int launch_decoder_tokens(const DecWeights& w, const DecState& s, int boxes, int
 // ------------------------------------------------------------------------------------------------ token -> image
 // 7 queries x 4096 keys per (box, head), internal dim 128 = 8 heads x 16 (downsample_rate 2, transformer.py:204-206).
 // kv rows: [4096][ld] fp32 with k at column 0 and v at column 128 (+ head*16); box_stride 0 when all boxes share keys.
+// box_img != null: the keys of box b are those of image box_img[b] (kv + box_img[b] * box_stride), shared by its boxes.
 __global__ void __launch_bounds__(256) decoder_t2i_kernel(const float* __restrict__ q, const float* __restrict__ kv,
-                                                          long long box_stride, int ld, float* __restrict__ out) {
+                                                          long long box_stride, int ld, const int* __restrict__ box_img,
+                                                          float* __restrict__ out) {
   const int box = blockIdx.x >> 3, h = blockIdx.x & 7, tid = threadIdx.x;
   __shared__ float qs[NT][16];
   __shared__ float red_m[8][NT];
@@ -264,7 +266,7 @@ __global__ void __launch_bounds__(256) decoder_t2i_kernel(const float* __restric
   if (tid < NT * 16)  // 1/sqrt(16) and log2(e) folded into q
     qs[tid / 16][tid % 16] = q[(size_t)box * NT * 128 + (tid / 16) * 128 + h * 16 + tid % 16] * (0.25f * 1.4426950408889634f);
   __syncthreads();
-  const float* base = kv + (size_t)box * box_stride + h * 16;
+  const float* base = kv + (size_t)(box_img ? box_img[box] : box) * box_stride + h * 16;
   float m[NT], l[NT], acc[NT][16];
 #pragma unroll
   for (int t = 0; t < NT; ++t) {
@@ -338,8 +340,9 @@ __global__ void __launch_bounds__(256) decoder_t2i_kernel(const float* __restric
   }
 }
 
-int launch_decoder_t2i(const float* q, const float* kv, long long box_stride, int ld, float* out, int boxes, cudaStream_t st) {
-  decoder_t2i_kernel<<<boxes * 8, 256, 0, st>>>(q, kv, box_stride, ld, out);
+int launch_decoder_t2i(const float* q, const float* kv, long long box_stride, int ld, const int* box_img, float* out,
+                       int boxes, cudaStream_t st) {
+  decoder_t2i_kernel<<<boxes * 8, 256, 0, st>>>(q, kv, box_stride, ld, box_img, out);
   CUDA_TRY(cudaGetLastError());
   return 0;
 }
@@ -348,7 +351,8 @@ int launch_decoder_t2i(const float* q, const float* kv, long long box_stride, in
 // Every image token attends to the 7 tokens (8 heads x 16). q: column `qcol` of the kvq rows (stride ld, box_stride 0
 // when shared); kv: [box][2][7][128]. out: [box*4096][128] fp32, the A operand of the out_proj GEMM.
 __global__ void __launch_bounds__(256) decoder_i2t_kernel(const float* __restrict__ qsrc, long long box_stride, int ld, int qcol,
-                                                          const float* __restrict__ kv, float* __restrict__ out) {
+                                                          const int* __restrict__ box_img, const float* __restrict__ kv,
+                                                          float* __restrict__ out) {
   const int box = blockIdx.y, tid = threadIdx.x;
   __shared__ float ks[NT * 128], vs[NT * 128];
   for (int i = tid; i < NT * 128; i += 256) {
@@ -357,7 +361,8 @@ __global__ void __launch_bounds__(256) decoder_i2t_kernel(const float* __restric
   }
   __syncthreads();
   const int pix = blockIdx.x * 32 + (tid >> 3), h = tid & 7;
-  const float4* qr = reinterpret_cast<const float4*>(qsrc + (size_t)box * box_stride + (size_t)pix * ld + qcol + h * 16);
+  const float4* qr = reinterpret_cast<const float4*>(qsrc + (size_t)(box_img ? box_img[box] : box) * box_stride +
+                                                     (size_t)pix * ld + qcol + h * 16);
   float qv[16];
 #pragma unroll
   for (int i = 0; i < 4; ++i) {
@@ -391,9 +396,9 @@ __global__ void __launch_bounds__(256) decoder_i2t_kernel(const float* __restric
   for (int i = 0; i < 4; ++i) dst[i] = make_float4(o[4 * i], o[4 * i + 1], o[4 * i + 2], o[4 * i + 3]);
 }
 
-int launch_decoder_i2t(const float* qsrc, long long box_stride, int ld, int qcol, const float* kv, float* out, int boxes,
-                       cudaStream_t st) {
-  decoder_i2t_kernel<<<dim3(128, boxes), 256, 0, st>>>(qsrc, box_stride, ld, qcol, kv, out);
+int launch_decoder_i2t(const float* qsrc, long long box_stride, int ld, int qcol, const int* box_img, const float* kv,
+                       float* out, int boxes, cudaStream_t st) {
+  decoder_i2t_kernel<<<dim3(128, boxes), 256, 0, st>>>(qsrc, box_stride, ld, qcol, box_img, kv, out);
   CUDA_TRY(cudaGetLastError());
   return 0;
 }
@@ -406,13 +411,33 @@ __global__ void __launch_bounds__(256) decoder_keys0_kernel(const float* __restr
   __shared__ float tile[32][33];
   const int t0 = blockIdx.x * 32, c0 = blockIdx.y * 32;
   const int tx = threadIdx.x & 31, ty = threadIdx.x >> 5;
+  emb += (size_t)blockIdx.z * E * 4096;
+  keys += (size_t)blockIdx.z * 4096 * E;
   for (int i = ty; i < 32; i += 8) tile[i][tx] = emb[(size_t)(c0 + i) * 4096 + t0 + tx];
   __syncthreads();
   for (int i = ty; i < 32; i += 8) keys[(size_t)(t0 + i) * E + c0 + tx] = tile[tx][i] + nomask[c0 + tx];
 }
 
-int launch_decoder_keys0(const float* emb, const float* nomask, float* keys, cudaStream_t st) {
-  decoder_keys0_kernel<<<dim3(128, 8), 256, 0, st>>>(emb, nomask, keys);
+// emb: [B][256][4096] (NCHW embeddings); keys: [B][4096][256]
+int launch_decoder_keys0(const float* emb, const float* nomask, float* keys, int B, cudaStream_t st) {
+  decoder_keys0_kernel<<<dim3(128, 8, B), 256, 0, st>>>(emb, nomask, keys);
+  CUDA_TRY(cudaGetLastError());
+  return 0;
+}
+
+// box_img[k] = image that box k belongs to; boxes are grouped by image, image i owns boxes [start[i], start[i+1]).
+__global__ void box_image_index_kernel(const BoxSegments seg, int* __restrict__ box_img) {
+  const int k = blockIdx.x * blockDim.x + threadIdx.x;
+  if (k >= seg.start[seg.n]) return;
+  int i = 0;
+  while (i + 1 < seg.n && k >= seg.start[i + 1]) ++i;
+  box_img[k] = i;
+}
+
+int launch_box_image_index(const BoxSegments& seg, int* box_img, cudaStream_t st) {
+  const int total = seg.start[seg.n];
+  if (total <= 0) return 0;
+  box_image_index_kernel<<<(total + 255) / 256, 256, 0, st>>>(seg, box_img);
   CUDA_TRY(cudaGetLastError());
   return 0;
 }

@@ -37,11 +37,20 @@ struct DecState {
   float* iou;          // [K]
 };
 
+// Boxes of a batch of images, grouped by image: image i owns boxes [start[i], start[i+1]); passed to kernels by value.
+constexpr int kMaxDecodeImages = 64;
+struct BoxSegments {
+  int n;
+  int start[kMaxDecodeImages + 1];
+};
+
 int launch_decoder_tokens(const DecWeights& w, const DecState& s, int boxes, int phase, int layer, cudaStream_t st);
-int launch_decoder_t2i(const float* q, const float* kv, long long box_stride, int ld, float* out, int boxes, cudaStream_t st);
-int launch_decoder_i2t(const float* qsrc, long long box_stride, int ld, int qcol, const float* kv, float* out, int boxes,
-                       cudaStream_t st);
-int launch_decoder_keys0(const float* emb, const float* nomask, float* keys, cudaStream_t st);
+int launch_decoder_t2i(const float* q, const float* kv, long long box_stride, int ld, const int* box_img, float* out,
+                       int boxes, cudaStream_t st);
+int launch_decoder_i2t(const float* qsrc, long long box_stride, int ld, int qcol, const int* box_img, const float* kv,
+                       float* out, int boxes, cudaStream_t st);
+int launch_decoder_keys0(const float* emb, const float* nomask, float* keys, int B, cudaStream_t st);
+int launch_box_image_index(const BoxSegments& seg, int* box_img, cudaStream_t st);
 int launch_dense_pe(const float* gauss, float* pe, cudaStream_t st);
 
 }  // namespace inksam

@@ -492,10 +492,16 @@ extern "C" int inksam_encode(inksam_handle* h, const void* images, int dtype, in
 // ================================================================================================ decode
 namespace {
 
-constexpr int kBoxChunk = 64;  // boxes decoded per pass (bounds the workspace at ~1.1 GB)
+constexpr int kBoxChunk = 128;  // boxes decoded per pass (bounds the workspace at ~2.2 GB)
 
-int decode_chunk(inksam_handle* h, const float* keys0, const float* kvq0, char* ws, const float* boxes, int n, int in_h,
-                 int in_w, int H, int W, uint8_t* masks, float* iou, float* low, float* logits, float thr, cudaStream_t st) {
+// Per-image geometry of a decode batch (host side).
+struct ImgGeom { int in_h, in_w, H, W; size_t mask_off; };  // mask_off: element offset of the image's first mask
+
+// One pass over boxes [k0, k0+n) of the batch.  keys0 / kvq0: per-image layer-0 keys and their merged k|v|q projection;
+// box_img: device array, image index of every box of the batch.
+int decode_chunk(inksam_handle* h, const float* keys0, const float* kvq0, char* ws, const float* boxes, const int* box_img,
+                 int k0, int n, const BoxSegments& seg, const std::vector<ImgGeom>& geom, uint8_t* masks, float* iou,
+                 float* low, float* logits, float thr, cudaStream_t st) {
   const std::string T = "mask_decoder.transformer.layers.";
   // per-chunk buffers
   size_t off = 0;
@@ -504,27 +510,29 @@ int decode_chunk(inksam_handle* h, const float* keys0, const float* kvq0, char* 
   float* kvq = reinterpret_cast<float*>(take((size_t)n * 4096 * 384 * 4));   // also holds the 128x128x64 upscaled map
   float* a1 = reinterpret_cast<float*>(take((size_t)n * 4096 * 128 * 4));
   DecState s{};
-  s.boxes = boxes;
+  s.boxes = boxes + 4 * (size_t)k0;
   s.queries = reinterpret_cast<float*>(take((size_t)n * 7 * 256 * 4));
   s.query_pe = reinterpret_cast<float*>(take((size_t)n * 7 * 256 * 4));
   s.q_t2i = reinterpret_cast<float*>(take((size_t)n * 7 * 128 * 4));
   s.attn_t2i = reinterpret_cast<float*>(take((size_t)n * 7 * 128 * 4));
   s.kv_i2t = reinterpret_cast<float*>(take((size_t)n * 2 * 7 * 128 * 4));
   s.hyper = reinterpret_cast<float*>(take((size_t)n * 32 * 4));
-  s.iou = iou;
+  s.iou = iou + k0;
+  low += (size_t)k0 * 65536;
+  const int* bimg = box_img + k0;
   const int Mb = n * 4096;
 
   auto tokens = [&](int phase, int layer) { ++h->launches; return launch_decoder_tokens(h->dec, s, n, phase, layer, st); };
-  auto t2i = [&](const float* kv, long long stride, int ld) {
+  auto t2i = [&](const float* kv, long long stride, int ld, const int* bi) {
     ++h->launches;
-    return launch_decoder_t2i(s.q_t2i, kv, stride, ld, s.attn_t2i, n, st);
+    return launch_decoder_t2i(s.q_t2i, kv, stride, ld, bi, s.attn_t2i, n, st);
   };
-  auto i2t = [&](const float* q, long long stride) {
+  auto i2t = [&](const float* q, long long stride, const int* bi) {
     ++h->launches;
-    return launch_decoder_i2t(q, stride, 384, 256, s.kv_i2t, a1, n, st);
+    return launch_decoder_i2t(q, stride, 384, 256, bi, s.kv_i2t, a1, n, st);
   };
   // keys <- norm4(keys + out_proj(image->token attention))   (transformer.py:176-180)
-  auto keys_update = [&](int layer, const float* resid, int resid_mod) -> int {
+  auto keys_update = [&](int layer, const float* resid, int resid_mod, const int* row_img) -> int {
     const float *ow, *ob, *nw, *nb;
     INK_TRY(need_f32(h, T + std::to_string(layer) + ".cross_attn_image_to_token.out_proj.weight", &ow));
     INK_TRY(need_f32(h, T + std::to_string(layer) + ".cross_attn_image_to_token.out_proj.bias", &ob));
@@ -532,16 +540,16 @@ int decode_chunk(inksam_handle* h, const float* keys0, const float* kvq0, char* 
     INK_TRY(need_f32(h, T + std::to_string(layer) + ".norm4.bias", &nb));
     G c; c.tf32 = 1; c.epi = EPI_RESID_LN_F32; c.A = a1; c.lda = 128; c.W = ow; c.ldw = 128;
     c.g.M = Mb; c.g.N = 256; c.g.K = 128; c.g.ldo = 256; c.g.out = keysb; c.g.bias = ob; c.g.resid = resid;
-    c.g.resid_mod = resid_mod; c.g.ln_w = nw; c.g.ln_b = nb; c.g.ln_eps = 1e-5f;
+    c.g.resid_mod = resid_mod; c.g.row_img = row_img; c.g.ln_w = nw; c.g.ln_b = nb; c.g.ln_eps = 1e-5f;
     return run_gemm(h, c, st);
   };
 
-  // ---- layer 0: the image-side k / v / q are shared by all boxes (kvq0)
+  // ---- layer 0: the image-side k / v / q are shared by all boxes of an image (kvq0)
   INK_TRY(tokens(0, 0));
-  INK_TRY(t2i(kvq0, 0, 384));
+  INK_TRY(t2i(kvq0, 4096LL * 384, 384, bimg));
   INK_TRY(tokens(2, 0));
-  INK_TRY(i2t(kvq0, 0));
-  INK_TRY(keys_update(0, keys0, 4096));
+  INK_TRY(i2t(kvq0, 4096LL * 384, bimg));
+  INK_TRY(keys_update(0, keys0, 4096, bimg));
   // ---- layer 1: per-box keys
   {
     G c; c.tf32 = 1; c.bn = 128; c.epi = EPI_BIAS_ROWADD_F32; c.A = keysb; c.lda = 256; c.W = h->wkvq[1]; c.ldw = 256;
@@ -550,10 +558,10 @@ int decode_chunk(inksam_handle* h, const float* keys0, const float* kvq0, char* 
     INK_TRY(run_gemm(h, c, st));
   }
   INK_TRY(tokens(1, 1));
-  INK_TRY(t2i(kvq, 4096LL * 384, 384));
+  INK_TRY(t2i(kvq, 4096LL * 384, 384, nullptr));
   INK_TRY(tokens(2, 1));
-  INK_TRY(i2t(kvq, 4096LL * 384));
-  INK_TRY(keys_update(1, keysb, 0));
+  INK_TRY(i2t(kvq, 4096LL * 384, nullptr));
+  INK_TRY(keys_update(1, keysb, 0, nullptr));
   // ---- final token -> image attention
   {
     G c; c.tf32 = 1; c.epi = EPI_BIAS_ROWADD_F32; c.A = keysb; c.lda = 256; c.W = h->wkvf; c.ldw = 256;
@@ -562,7 +570,7 @@ int decode_chunk(inksam_handle* h, const float* keys0, const float* kvq0, char* 
     INK_TRY(run_gemm(h, c, st));
   }
   INK_TRY(tokens(3, 0));
-  INK_TRY(t2i(kvq, 4096LL * 256, 256));
+  INK_TRY(t2i(kvq, 4096LL * 256, 256, nullptr));
   INK_TRY(tokens(4, 0));
   // ---- upscaling: ConvT(256->64,k2,s2)+LayerNorm2d+GELU, ConvT(64->32,k2,s2)+GELU, dot with the hypernetwork vector
   const float *u0w, *u0b, *u1w, *u1b, *u3w, *u3b;
@@ -584,57 +592,90 @@ int decode_chunk(inksam_handle* h, const float* keys0, const float* kvq0, char* 
     c.g.M = n * 16384; c.g.N = 128; c.g.K = 64; c.g.ldo = 128; c.g.out = low; c.g.bias = u3b; c.g.hyper = s.hyper;
     INK_TRY(run_gemm(h, c, st));
   }
-  // ---- fused upsample + crop + resize + threshold
-  ++h->launches;
-  {
-    Prof p(h, CAT_POST, (double)n * (65536.0 * 4 + (double)H * W * ((masks ? 1 : 0) + (logits ? 4 : 0))), st);
-    INK_TRY(launch_postprocess(low, masks, logits, n, in_h, in_w, H, W, thr, st));
+  // ---- fused upsample + crop + resize + threshold: one launch per image that has boxes in this chunk
+  for (int i = 0; i < seg.n; ++i) {
+    const int b0 = seg.start[i] > k0 ? seg.start[i] : k0;
+    const int b1 = seg.start[i + 1] < k0 + n ? seg.start[i + 1] : k0 + n;
+    if (b1 <= b0) continue;
+    const ImgGeom& gm = geom[i];
+    const size_t HW = (size_t)gm.H * gm.W;
+    const size_t mo = gm.mask_off + (size_t)(b0 - seg.start[i]) * HW;
+    ++h->launches;
+    Prof p(h, CAT_POST, (double)(b1 - b0) * (65536.0 * 4 + (double)HW * ((masks ? 1 : 0) + (logits ? 4 : 0))), st);
+    INK_TRY(launch_postprocess(low + (size_t)(b0 - k0) * 65536, masks ? masks + mo : nullptr, logits ? logits + mo : nullptr,
+                               b1 - b0, gm.in_h, gm.in_w, gm.H, gm.W, thr, st));
   }
   return 0;
 }
 
 }  // namespace
 
-extern "C" int inksam_decode_boxes(inksam_handle* h, const float* embedding, const float* boxes, int K, int in_h, int in_w,
-                                   int orig_h, int orig_w, uint8_t* masks_out, float* iou_out, float* lowres_out,
-                                   float* logits_out, float mask_threshold, void* stream) {
-  if (!h || !embedding || !iou_out || !lowres_out) return set_error("inksam_decode_boxes: null argument");
-  if (!h->finalized) return set_error("inksam_decode_boxes: weights not finalized (call inksam_finalize_weights)");
-  if (K < 0) return set_error("inksam_decode_boxes: K=%d", K);
+extern "C" int inksam_decode_batch(inksam_handle* h, const float* embeddings, int B, const float* boxes, const int* counts,
+                                   const int* in_hw, const int* orig_hw, uint8_t* masks_out, float* iou_out,
+                                   float* lowres_out, float* logits_out, float mask_threshold, void* stream) {
+  if (!h || !embeddings || !counts || !in_hw || !orig_hw || !iou_out || !lowres_out)
+    return set_error("inksam_decode_batch: null argument");
+  if (!h->finalized) return set_error("inksam_decode_batch: weights not finalized (call inksam_finalize_weights)");
+  if (B < 1 || B > kMaxDecodeImages) return set_error("inksam_decode_batch: B=%d not in 1..%d", B, kMaxDecodeImages);
+  BoxSegments seg{};
+  seg.n = B;
+  std::vector<ImgGeom> geom(B);
+  size_t moff = 0;
+  for (int i = 0; i < B; ++i) {
+    if (counts[i] < 0) return set_error("inksam_decode_batch: counts[%d]=%d", i, counts[i]);
+    seg.start[i + 1] = seg.start[i] + counts[i];
+    ImgGeom& gm = geom[i];
+    gm.in_h = in_hw[2 * i]; gm.in_w = in_hw[2 * i + 1]; gm.H = orig_hw[2 * i]; gm.W = orig_hw[2 * i + 1];
+    if (gm.in_h < 1 || gm.in_w < 1 || gm.in_h > 1024 || gm.in_w > 1024 || gm.H < 1 || gm.W < 1)
+      return set_error("inksam_decode_batch: image %d: bad sizes input %dx%d original %dx%d", i, gm.in_h, gm.in_w, gm.H, gm.W);
+    gm.mask_off = moff;
+    moff += (size_t)counts[i] * gm.H * gm.W;
+  }
+  const int K = seg.start[B];
   if (K == 0) return 0;
-  if (!boxes) return set_error("inksam_decode_boxes: null boxes");
-  if (in_h < 1 || in_w < 1 || in_h > 1024 || in_w > 1024 || orig_h < 1 || orig_w < 1)
-    return set_error("inksam_decode_boxes: bad sizes input %dx%d original %dx%d", in_h, in_w, orig_h, orig_w);
+  if (!boxes) return set_error("inksam_decode_batch: null boxes");
   CUDA_TRY(cudaSetDevice(h->device));
   auto st = static_cast<cudaStream_t>(stream);
   struct CatGuard { inksam_handle* h; CatGuard(inksam_handle* x) : h(x) { h->prof_cat = 1; } ~CatGuard() { h->prof_cat = 0; } } guard(h);
   const int nc = K < kBoxChunk ? K : kBoxChunk;
-  const size_t shared_bytes = align_up((size_t)4096 * 256 * 4) + align_up((size_t)4096 * 384 * 4);
+  const size_t sz_keys0 = align_up((size_t)B * 4096 * 256 * 4), sz_kvq0 = align_up((size_t)B * 4096 * 384 * 4);
+  const size_t sz_idx = align_up((size_t)K * 4);
+  const size_t shared_bytes = sz_keys0 + sz_kvq0 + sz_idx;
   const size_t chunk_bytes = align_up((size_t)nc * 4096 * 256 * 4) + align_up((size_t)nc * 4096 * 384 * 4) +
                              align_up((size_t)nc * 4096 * 128 * 4) + 8 * align_up((size_t)nc * 7 * 256 * 4);
   INK_TRY(grow(&h->dec_ws, &h->dec_ws_bytes, shared_bytes + chunk_bytes));
   char* ws = static_cast<char*>(h->dec_ws);
   float* keys0 = reinterpret_cast<float*>(ws);
-  float* kvq0 = reinterpret_cast<float*>(ws + align_up((size_t)4096 * 256 * 4));
-  const float* nomask;
+  float* kvq0 = reinterpret_cast<float*>(ws + sz_keys0);
+  int* box_img = reinterpret_cast<int*>(ws + sz_keys0 + sz_kvq0);
+  const float* nomask = nullptr;
   INK_TRY(need_f32(h, "prompt_encoder.no_mask_embed.weight", &nomask));
+  ++h->launches;
+  INK_TRY(launch_box_image_index(seg, box_img, st));
   // keys of layer 0 = embedding + dense no-mask prompt, token-major; their k / v / q projections once per image
   ++h->launches;
-  INK_TRY(launch_decoder_keys0(embedding, nomask, keys0, st));
+  INK_TRY(launch_decoder_keys0(embeddings, nomask, keys0, B, st));
   {
     G c; c.tf32 = 1; c.bn = 128; c.epi = EPI_BIAS_ROWADD_F32; c.A = keys0; c.lda = 256; c.W = h->wkvq[0]; c.ldw = 256;
-    c.g.M = 4096; c.g.N = 384; c.g.K = 256; c.g.ldo = 384; c.g.out = kvq0; c.g.bias = h->bkvq[0]; c.g.rowadd = h->ra[0];
+    c.g.M = B * 4096; c.g.N = 384; c.g.K = 256; c.g.ldo = 384; c.g.out = kvq0; c.g.bias = h->bkvq[0]; c.g.rowadd = h->ra[0];
     c.g.rowadd_mod = 4096;
     INK_TRY(run_gemm(h, c, st));
   }
-  const size_t HW = (size_t)orig_h * orig_w;
   for (int k0 = 0; k0 < K; k0 += kBoxChunk) {
     const int n = K - k0 < kBoxChunk ? K - k0 : kBoxChunk;
-    INK_TRY(decode_chunk(h, keys0, kvq0, ws + shared_bytes, boxes + 4 * k0, n, in_h, in_w, orig_h, orig_w,
-                         masks_out ? masks_out + k0 * HW : nullptr, iou_out + k0, lowres_out + (size_t)k0 * 65536,
-                         logits_out ? logits_out + k0 * HW : nullptr, mask_threshold, st));
+    INK_TRY(decode_chunk(h, keys0, kvq0, ws + shared_bytes, boxes, box_img, k0, n, seg, geom, masks_out, iou_out, lowres_out,
+                         logits_out, mask_threshold, st));
   }
   return 0;
+}
+
+extern "C" int inksam_decode_boxes(inksam_handle* h, const float* embedding, const float* boxes, int K, int in_h, int in_w,
+                                   int orig_h, int orig_w, uint8_t* masks_out, float* iou_out, float* lowres_out,
+                                   float* logits_out, float mask_threshold, void* stream) {
+  if (K < 0) return set_error("inksam_decode_boxes: K=%d", K);
+  const int counts[1] = {K}, in_hw[2] = {in_h, in_w}, orig_hw[2] = {orig_h, orig_w};
+  return inksam_decode_batch(h, embedding, 1, boxes, counts, in_hw, orig_hw, masks_out, iou_out, lowres_out, logits_out,
+                             mask_threshold, stream);
 }
 
 // ================================================================================================ profiling

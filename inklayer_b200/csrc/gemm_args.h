@@ -33,6 +33,7 @@ struct GemmArgs {
   const float* hyper;  // EPI_UPSCALE2_MASK: [boxes][32]
   int win_remap;       // EPI_BIAS_BF16: store token rows in 14x14-window order (windowed encoder blocks)
   int resid_mod;       // EPI_RESID_LN_F32: resid row = m % resid_mod when non-zero (keys shared by all boxes)
+  const int* row_img;  // EPI_RESID_LN_F32 with resid_mod: resid row += row_img[m / resid_mod] * resid_mod (keys of the box's image)
 };
 
 }  // namespace inksam

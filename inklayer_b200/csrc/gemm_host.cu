@@ -81,10 +81,7 @@ static int launch_one(const CUtensorMap& tA, const CUtensorMap& tB, const GemmAr
     attr_done = true;
   }
   const int tiles = ((g.M + C::BM * CG - 1) / (C::BM * CG)) * ((g.N + BN - 1) / BN);
-  int clusters = num_sms / CG;
-  if (tiles < clusters) clusters = tiles;
   cudaLaunchConfig_t cfg{};
-  cfg.gridDim = dim3(clusters * CG);
   cfg.blockDim = dim3(384);
   cfg.dynamicSmemBytes = C::SMEM_BYTES;
   cfg.stream = st;
@@ -95,6 +92,20 @@ static int launch_one(const CUtensorMap& tA, const CUtensorMap& tB, const GemmAr
   attr[0].val.clusterDim.z = 1;
   cfg.attrs = attr;
   cfg.numAttrs = 1;
+  // The tile loop is statically strided over the resident clusters, so the grid must not exceed what is
+  // co-resident: CTA pairs need both SMs of a TPC, and not every SM of the 148 can be paired on every part.
+  static int max_clusters = 0;
+  if (max_clusters == 0) {
+    max_clusters = num_sms / CG;
+    if (CG > 1) {
+      cfg.gridDim = dim3((num_sms / CG) * CG);
+      int n = 0;
+      if (cudaOccupancyMaxActiveClusters(&n, kern, &cfg) == cudaSuccess && n > 0 && n < max_clusters) max_clusters = n;
+    }
+  }
+  int clusters = max_clusters;
+  if (tiles < clusters) clusters = tiles;
+  cfg.gridDim = dim3(clusters * CG);
   CUDA_TRY(cudaLaunchKernelEx(&cfg, kern, tA, tB, g));
   return 0;
 }

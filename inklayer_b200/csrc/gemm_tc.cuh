@@ -294,7 +294,8 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
           tmem_ld_32x32(taddr + c * 32, v);
           tmem_ld_wait();
           if constexpr (EPI == EPI_RESID_LN_F32) {
-            const int mm = row_ok ? (g.resid_mod ? m % g.resid_mod : m) : 0;
+            int mm = row_ok ? (g.resid_mod ? m % g.resid_mod : m) : 0;
+            if (g.row_img != nullptr && row_ok) mm += __ldg(g.row_img + m / g.resid_mod) * g.resid_mod;
             const float* r = g.resid + (size_t)mm * g.ldo + c * 32;
 #pragma unroll
             for (int h = 0; h < 4; ++h) {

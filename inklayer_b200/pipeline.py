@@ -7,7 +7,9 @@ throughput form used by `main.py --dir`-style drivers: B sketches are encoded in
 is decoded, masks return as numpy bool arrays."""
 from __future__ import annotations
 
-from typing import List, Optional, Sequence
+from collections import deque
+from concurrent.futures import ThreadPoolExecutor
+from typing import Iterable, Iterator, List, Optional, Sequence, Tuple
 
 import numpy as np
 import torch
@@ -17,63 +19,124 @@ from .resize import ResizeLongestSide
 from .sam import Sam, build_sam
 
 
+class _Slot:
+    """One in-flight batch: pinned input staging, device input, device + pinned mask buffers, and its three events."""
+
+    def __init__(self, sam: Sam, max_batch: int) -> None:
+        S = sam.image_encoder.img_size
+        self.host_img = torch.empty((max_batch, S, S, 3), dtype=torch.uint8).pin_memory()
+        self.dev_img = torch.empty((max_batch, S, S, 3), dtype=torch.uint8, device=sam.device)
+        self.dev_masks: Optional[torch.Tensor] = None
+        self.host_masks: Optional[torch.Tensor] = None
+        self.ev_in, self.ev_done, self.ev_out = torch.cuda.Event(), torch.cuda.Event(), torch.cuda.Event()
+        self.views: list = []
+
+    def mask_buffers(self, nbytes: int, device) -> None:
+        if self.dev_masks is None or self.dev_masks.numel() < nbytes:
+            self.dev_masks = torch.empty(nbytes, dtype=torch.uint8, device=device)
+            self.host_masks = torch.empty(nbytes, dtype=torch.uint8).pin_memory()
+
+
 class SketchSegmenter:
-    def __init__(self, sam: Sam, max_batch: int = 8) -> None:
+    """Batched, pipelined form of run_SAM for `main.py --dir`-style drivers (main.py:27-32 loops run_SAM per file).
+
+    Each batch of up to `max_batch` sketches is encoded in one pass and every box of every sketch is decoded in one
+    pass.  `depth` batches are in flight: the pinned-memory H2D copy of batch i+1 and the D2H copy + host hand-off of
+    batch i-1 run on their own streams / a worker thread under the kernels of batch i."""
+
+    def __init__(self, sam: Sam, max_batch: int = 8, depth: int = 2) -> None:
         if sam.device.type != "cuda":
             raise RuntimeError("SketchSegmenter needs a Sam on a CUDA device")
         self.sam = sam
         self.transform = ResizeLongestSide(sam.image_encoder.img_size)
         self.max_batch = max_batch
-        S = sam.image_encoder.img_size
-        self._host_img = torch.empty((max_batch, S, S, 3), dtype=torch.uint8).pin_memory()
-        self._dev_img = torch.empty((max_batch, S, S, 3), dtype=torch.uint8, device=sam.device)
-        self._host_masks: Optional[torch.Tensor] = None
+        self.depth = max(1, depth)
+        self._slots = [_Slot(sam, max_batch) for _ in range(self.depth + 1)]
+        with torch.cuda.device(sam.device):
+            self._s_in, self._s_run, self._s_out = torch.cuda.Stream(), torch.cuda.Stream(), torch.cuda.Stream()
+        self._pool = ThreadPoolExecutor(max_workers=1)
+        self._next = 0
         self.h2d_bytes = 0
         self.d2h_bytes = 0
 
-    def _mask_staging(self, nbytes: int) -> torch.Tensor:
-        if self._host_masks is None or self._host_masks.numel() < nbytes:
-            self._host_masks = torch.empty(nbytes, dtype=torch.uint8).pin_memory()
-        return self._host_masks
+    # ------------------------------------------------------------------ one batch: enqueue everything, no host sync
+    def _submit(self, images: Sequence[np.ndarray], boxes: Sequence[np.ndarray]) -> _Slot:
+        sam, dev, B = self.sam, self.sam.device, len(images)
+        if B < 1 or B > self.max_batch:
+            raise RuntimeError(f"a batch holds 1..{self.max_batch} sketches, got {B}")
+        slot = self._slots[self._next]
+        self._next = (self._next + 1) % len(self._slots)
+        sizes, in_sizes = [], []
+        for i, im in enumerate(images):
+            r = self.transform.apply_image(im)  # host resize (Pillow, exact), identity at 1024x1024
+            h, w = r.shape[:2]
+            slot.host_img[i, :h, :w].copy_(torch.from_numpy(r))
+            sizes.append(tuple(int(v) for v in im.shape[:2]))
+            in_sizes.append((h, w))
+        tbs = [self.transform.apply_boxes_torch(torch.as_tensor(np.asarray(bx, dtype=np.float32).reshape(-1, 4)), sizes[i])
+               for i, bx in enumerate(boxes)]
+        hb = torch.cat(tbs).pin_memory() if sum(len(t) for t in tbs) else torch.zeros((0, 4))
+        total = sum(len(t) * s[0] * s[1] for t, s in zip(tbs, sizes))
+        slot.mask_buffers(max(total, 1), dev)
+        caller = torch.cuda.current_stream(dev)
+        self._s_in.wait_stream(caller)
+        with torch.cuda.stream(self._s_in):
+            slot.dev_img[:B].copy_(slot.host_img[:B], non_blocking=True)
+            db = hb.to(dev, non_blocking=True)
+            slot.ev_in.record()
+        self.h2d_bytes += B * slot.host_img[0].numel() + hb.numel() * 4
+        with torch.cuda.stream(self._s_run):
+            self._s_run.wait_event(slot.ev_in)
+            feats = sam.encode(slot.dev_img[:B], in_sizes)
+            counts = [len(t) for t in tbs]
+            splits = list(torch.split(db, counts)) if db.numel() else [db[:0] for _ in tbs]
+            _, _, _, offs = sam.decode_batch(feats, splits, in_sizes, sizes, masks_out=slot.dev_masks)
+            db.record_stream(self._s_run)
+            slot.ev_done.record()
+        with torch.cuda.stream(self._s_out):
+            self._s_out.wait_event(slot.ev_done)
+            slot.host_masks[:total].copy_(slot.dev_masks[:total], non_blocking=True)
+            slot.ev_out.record()
+        self.d2h_bytes += total
+        slot.views = [(offs[i], counts[i], sizes[i]) for i in range(B)]
+        return slot
+
+    @staticmethod
+    def _collect(slot: _Slot) -> List[np.ndarray]:
+        """Waits for the batch's D2H copy and hands every image's masks to the caller as its own bool array."""
+        slot.ev_out.synchronize()
+        host = slot.host_masks.numpy()
+        out = []
+        for off, k, (H, W) in slot.views:
+            out.append(host[off:off + k * H * W].view(np.bool_).reshape(k, H, W).copy())
+        return out
+
+    # ------------------------------------------------------------------ public API
+    @torch.no_grad()
+    def segment_stream(self, batches: Iterable[Tuple[Sequence[np.ndarray], Sequence[np.ndarray]]]) -> Iterator[List[np.ndarray]]:
+        """batches: iterable of (images, boxes) with up to max_batch sketches each (see segment_batch for the element
+        types).  Yields, in order, one list of bool arrays [K_i,H,W] per batch; results trail the input by `depth`
+        batches so that copies overlap compute."""
+        pending: deque = deque()
+        for images, boxes in batches:
+            assert len(images) == len(boxes)
+            pending.append(self._pool.submit(self._collect, self._submit(images, boxes)))
+            if len(pending) > self.depth:
+                yield pending.popleft().result()
+        while pending:
+            yield pending.popleft().result()
 
     @torch.no_grad()
     def segment_batch(self, images: Sequence[np.ndarray], boxes: Sequence[np.ndarray]) -> List[np.ndarray]:
         """images: uint8 [H,W,3] each (RGB as the model should see it); boxes: float [K_i,4] pixel xyxy in the ORIGINAL
         frame of image i.  Returns one bool array [K_i,H,W] per image."""
         assert len(images) == len(boxes)
+        chunks = ((images[b0:b0 + self.max_batch], boxes[b0:b0 + self.max_batch])
+                  for b0 in range(0, len(images), self.max_batch))
         out: List[np.ndarray] = []
-        for b0 in range(0, len(images), self.max_batch):
-            out.extend(self._segment_chunk(images[b0:b0 + self.max_batch], boxes[b0:b0 + self.max_batch]))
+        for res in self.segment_stream(chunks):
+            out.extend(res)
         return out
-
-    def _segment_chunk(self, images, boxes) -> List[np.ndarray]:
-        dev, B = self.sam.device, len(images)
-        sizes, in_sizes = [], []
-        for i, im in enumerate(images):
-            r = self.transform.apply_image(im)  # host resize, identity at 1024x1024
-            h, w = r.shape[:2]
-            self._host_img[i, :h, :w].copy_(torch.from_numpy(r))
-            sizes.append(tuple(im.shape[:2]))
-            in_sizes.append((h, w))
-        self._dev_img[:B].copy_(self._host_img[:B], non_blocking=True)
-        self.h2d_bytes += B * self._host_img[0].numel()
-        feats = self.sam.encode(self._dev_img[:B], in_sizes)
-        total = sum(int(len(bx)) * s[0] * s[1] for bx, s in zip(boxes, sizes))
-        stage = self._mask_staging(max(total, 1))
-        views, off = [], 0
-        for i in range(B):
-            bx = torch.as_tensor(np.asarray(boxes[i], dtype=np.float32).reshape(-1, 4))
-            tb = self.transform.apply_boxes_torch(bx, sizes[i]).to(dev, non_blocking=True)
-            self.h2d_bytes += tb.numel() * 4
-            masks, _, _ = self.sam.decode_boxes(feats[i], tb, in_sizes[i], sizes[i])
-            n = masks.numel()
-            stage[off:off + n].copy_(masks.view(torch.uint8).reshape(-1), non_blocking=True)
-            views.append((off, n, (masks.shape[0],) + sizes[i]))
-            off += n
-        self.d2h_bytes += off
-        torch.cuda.current_stream(dev).synchronize()
-        host = stage.numpy()
-        return [host[o:o + n].view(np.bool_).reshape(shape).copy() for o, n, shape in views]
 
 
 _default: Optional[SketchSegmenter] = None

@@ -188,6 +188,46 @@ class Sam:
         return (logits if return_logits else masks.view(torch.bool)), iou, low
 
 
+    @torch.no_grad()
+    def decode_batch(self, embeddings: torch.Tensor, boxes: Sequence[torch.Tensor], input_sizes: Sequence[Tuple[int, int]],
+                     original_sizes: Sequence[Tuple[int, int]], masks_out: Optional[torch.Tensor] = None):
+        """The boxes of B images in one pass of the decoder (the `main.py --dir` form of predict_torch).
+        embeddings: float32 [B,256,64,64]; boxes[i]: [K_i,4] xyxy in image i's input frame (device or host).
+        Returns (masks, iou [sum K], low_res [sum K,256,256], offsets) where `masks` is ONE flat uint8 device tensor
+        holding image after image K_i maps of original_sizes[i] (written into `masks_out` when given) and
+        offsets[i] is image i's first element."""
+        h = self._require()
+        dev, B = self.device, len(boxes)
+        if embeddings.shape[0] != B or len(input_sizes) != B or len(original_sizes) != B:
+            raise RuntimeError("decode_batch: embeddings, boxes and sizes disagree on the number of images")
+        emb = embeddings.to(device=dev, dtype=torch.float32).contiguous()
+        counts = (ctypes.c_int * B)(*[int(b.shape[0]) for b in boxes])
+        in_hw = (ctypes.c_int * (2 * B))(*[int(v) for s in input_sizes for v in s])
+        or_hw = (ctypes.c_int * (2 * B))(*[int(v) for s in original_sizes for v in s])
+        total = sum(counts)
+        offsets, n = [], 0
+        for i in range(B):
+            offsets.append(n)
+            n += counts[i] * int(original_sizes[i][0]) * int(original_sizes[i][1])
+        if all(b.device == dev for b in boxes):
+            bx = torch.cat([b.reshape(-1, 4).to(torch.float32) for b in boxes]).contiguous()
+        else:  # one pinned staging copy for all host boxes
+            hb = torch.cat([b.reshape(-1, 4).to(dtype=torch.float32, device="cpu") for b in boxes]).pin_memory()
+            bx = hb.to(dev, non_blocking=True)
+        if masks_out is None:
+            masks_out = torch.empty(max(n, 1), dtype=torch.uint8, device=dev)
+        elif masks_out.numel() < n or masks_out.dtype != torch.uint8 or masks_out.device != dev:
+            raise RuntimeError("decode_batch: masks_out must be a uint8 tensor on the model's device with room for all masks")
+        iou = torch.empty((total,), dtype=torch.float32, device=dev)
+        low = torch.empty((total, 256, 256), dtype=torch.float32, device=dev)
+        if total > 0:
+            with torch.cuda.device(dev):
+                _lib.check(_lib.load().inksam_decode_batch(
+                    h, _ptr(emb), B, _ptr(bx), counts, in_hw, or_hw, _ptr(masks_out), _ptr(iou), _ptr(low), _ptr(None),
+                    ctypes.c_float(self.mask_threshold), _stream(dev)))
+        return masks_out, iou, low, offsets
+
+
 # ---------------------------------------------------------------------------------------- factories
 def _build(name: str, checkpoint: Optional[str]) -> Sam:
     cfg = CONFIGS[name]
