@@ -93,12 +93,12 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
   }
   if (warp == 1 && lane == 0) {
     for (int s = 0; s < C::STAGES; ++s) {
-      mbar_init(full_bar(s), CG);  // CG == 2: leader's expect_tx arrive + peer's plain arrive
+      mbar_init(full_bar(s), 1);   // one expect_tx arrive (CG == 2: the leader's covers the bytes of both CTAs)
       mbar_init(empty_bar(s), 1);  // one tcgen05.commit
     }
     for (int s = 0; s < 2; ++s) {
       mbar_init(tfull_bar(s), 1);          // one tcgen05.commit
-      mbar_init(tempty_bar(s), 32 * gemm_epi_warps(EPI) * CG);  // every epilogue thread of the pair
+      mbar_init(tempty_bar(s), gemm_epi_warps(EPI) * CG);  // one arrive per epilogue warp of the pair
     }
     fence_mbar_init();
   }
@@ -138,8 +138,9 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
             tma_load_2d(b_dst, &tmB, full_bar(stage), k0, n0);
           } else {
             const uint32_t lead_full = mapa_u32(full_bar(stage), 0);
+            // The peer's bytes may land on the leader's barrier before this expect_tx; the phase still cannot complete
+            // without the leader's arrive, and the peer cannot run a phase ahead (it waits for the MMA's commit).
             if (leader) mbar_arrive_expect_tx(full_bar(stage), 2 * C::STAGE_BYTES);
-            else mbar_arrive_cluster(lead_full);
             if (g.a_conv3x3) {
               const int cpt = g.conv_c / C::KELEMS;
               const int tap = kb / cpt, c0 = (kb % cpt) * C::KELEMS;
@@ -434,8 +435,11 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
       }
 
       tc_fence_before();
-      if constexpr (CG == 1) mbar_arrive(tempty_bar(as));
-      else mbar_arrive_cluster(mapa_u32(tempty_bar(as), 0));
+      __syncwarp();
+      if (lane == 0) {
+        if constexpr (CG == 1) mbar_arrive(tempty_bar(as));
+        else mbar_arrive_cluster(mapa_u32(tempty_bar(as), 0));
+      }
       if (++as == 2) { as = 0; aphase ^= 1u; }
     }
   }

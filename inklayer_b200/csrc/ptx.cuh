@@ -60,7 +60,9 @@ __device__ __forceinline__ void mbar_arrive(uint32_t bar) {
 }
 // Arrive on a barrier that lives in another CTA of the cluster (address from mapa_u32).
 __device__ __forceinline__ void mbar_arrive_cluster(uint32_t bar_cluster_addr) {
-  asm volatile("mbarrier.arrive.release.cluster.shared::cluster.b64 _, [%0];" ::"r"(bar_cluster_addr) : "memory");
+  // relaxed: the arrive publishes no generic-proxy data (TMEM reads are ordered by tcgen05.wait::ld + tcgen05.fence);
+  // a .release.cluster here compiles to MEMBAR.ALL.GPU + ERRBAR in front of every arrive.
+  asm volatile("mbarrier.arrive.relaxed.cluster.shared::cluster.b64 _, [%0];" ::"r"(bar_cluster_addr) : "memory");
 }
 __device__ __forceinline__ void mbar_wait(uint32_t bar, uint32_t parity) {
   asm volatile(
