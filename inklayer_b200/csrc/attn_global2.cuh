@@ -1,0 +1,301 @@
+// Global (64x64-token) encoder attention, warp-specialised: replaces Attention.forward + add_decomposed_rel_pos for
+// the global blocks (SA/modeling/image_encoder.py:224-240,325-361; blocks 7/15/23/31 of ViT-H, build_sam.py:19).
+//
+// One CTA = 256 queries of one (image, head) = two 128-row tiles A and B that ping-pong through the tensor cores:
+//   warps 0-3   softmax group A (thread = query row = TMEM lane)       warps 4-7   softmax group B
+//   warp 10     TMA producer: Q tiles, rel-pos tables, then K and V tiles of 128 keys through two 2-slot rings
+//   warps 8, 9  MMA issuers (one thread each) of group A and group B: issuing ~13 tcgen05.mma per sub-tile is itself a
+//               serial cost (descriptor moves to uniform registers), so each group gets its own issuing thread.  The unit of work is a SUB-TILE t of 64 keys (= one row kh = t of the 64x64
+//               key grid, so the rel-pos row bias is a single scalar per query and sub-tile); S is double buffered
+//               per group, so S(t+1) is already in TMEM when softmax(t) ends and the MMAs never sit on a group's
+//               critical path.  Per group:   S(0) S(1), then for t = 0..63:  PV(t) S(t+2)
+// TMEM (512 columns): S_A0 [0,64) S_A1 [64,128) S_B0 [128,192) S_B1 [192,256)  O_A [256,336)  O_B [384,464);
+// P(t) (bf16) is written back over the first 32 columns of S(t).  The prologue borrows all 512 columns for the
+// rel-pos products T_h / T_w of both tiles (T[q][r] = q . rel_pos[r] on the UNSCALED q, image_encoder.py:234,354-355)
+// and the K ring for the tables.
+// Softmax follows attn_tc.cuh: exp2 with a fixed shift taken from the first 32 keys, exact rescale if a later key
+// exceeds it by 2^32 (cold path).
+#pragma once
+#include "attn_tc.cuh"
+
+namespace inksam {
+
+template <int HD>
+struct AttnGlobal2 {
+  static constexpr int TILE = AttnTile<HD>::bytes(128);  // 20480 (hd 80) or 16384 (hd 64)
+  static constexpr int BH_PITCH = 66;                     // floats per biasH row
+  static constexpr int OFF_Q = 0;                         // Q_A, Q_B
+  static constexpr int OFF_K = 2 * TILE;                  // K ring, 2 slots
+  static constexpr int OFF_V = 4 * TILE;                  // V ring, 2 slots
+  static constexpr int OFF_BH = 6 * TILE;                 // biasH [256][66] fp32
+  static constexpr int OFF_BAR = OFF_BH + 256 * BH_PITCH * 4;
+  static constexpr int SMEM_BYTES = OFF_BAR + 256 + 1024;
+  static constexpr int THREADS = 352;
+};
+
+template <int HD>
+__global__ void __launch_bounds__(352, 1)
+attn_global2_kernel(const __grid_constant__ CUtensorMap tm64, const __grid_constant__ CUtensorMap tm16,
+                    const __grid_constant__ CUtensorMap tr64, const __grid_constant__ CUtensorMap tr16, const AttnArgs a) {
+  using L = AttnGlobal2<HD>;
+  constexpr int TILE = L::TILE;
+  constexpr uint32_t TILE_TX = 128 * HD * 2;
+  constexpr uint32_t IDESC_T = make_idesc(1u, 128, 128);
+  constexpr uint32_t IDESC_S = make_idesc(1u, 128, 64);
+  constexpr int NT = 32;   // key tiles of 128 (TMA / smem ring granularity)
+  constexpr int NS = 64;   // sub-tiles of 64 keys (MMA / softmax granularity)
+
+  extern __shared__ uint8_t smem_raw[];
+  const uint32_t smem_base = (smem_u32(smem_raw) + 1023u) & ~1023u;
+  uint8_t* smem_gen = smem_raw + (smem_base - smem_u32(smem_raw));
+  auto q_tile = [&](int g) { return smem_base + L::OFF_Q + g * TILE; };
+  auto k_tile = [&](int s) { return smem_base + L::OFF_K + s * TILE; };
+  auto v_tile = [&](int s) { return smem_base + L::OFF_V + s * TILE; };
+  float* biasH = reinterpret_cast<float*>(smem_gen + L::OFF_BH);
+  const uint32_t bar0 = smem_base + L::OFF_BAR;
+  // barrier map (8 bytes each)
+  const uint32_t bar_q = bar0, bar_rel = bar0 + 8, bar_tdone = bar0 + 16, bar_tread = bar0 + 24;
+  auto bar_kfull = [&](int s) { return bar0 + 32 + 8 * s; };
+  auto bar_kempty = [&](int s) { return bar0 + 48 + 8 * s; };
+  auto bar_vfull = [&](int s) { return bar0 + 64 + 8 * s; };
+  auto bar_vempty = [&](int s) { return bar0 + 80 + 8 * s; };
+  auto bar_sfull = [&](int g, int buf) { return bar0 + 96 + 8 * (2 * g + buf); };
+  auto bar_pready = [&](int g, int buf) { return bar0 + 128 + 8 * (2 * g + buf); };
+  auto bar_pvdone = [&](int g, int buf) { return bar0 + 160 + 8 * (2 * g + buf); };
+  const uint32_t tmem_slot = bar0 + 192;
+  volatile uint32_t* tmem_slot_ptr = reinterpret_cast<volatile uint32_t*>(smem_gen + L::OFF_BAR + 192);
+
+  const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+  const int qp = blockIdx.x & 15;
+  const int head = (blockIdx.x >> 4) % a.heads;
+  const int b = (blockIdx.x >> 4) / a.heads;
+  const int row_q = b * 4096 + qp * 256;
+  const int col_q = head * HD, col_k = a.D + col_q, col_v = 2 * a.D + col_q;
+
+  if (tid == 0) {
+    mbar_init(bar_q, 1); mbar_init(bar_rel, 1); mbar_init(bar_tdone, 2); mbar_init(bar_tread, 8);
+    for (int s = 0; s < 2; ++s) {
+      mbar_init(bar_kfull(s), 1); mbar_init(bar_kempty(s), 2); mbar_init(bar_vfull(s), 1); mbar_init(bar_vempty(s), 2);
+      for (int buf = 0; buf < 2; ++buf) {
+        mbar_init(bar_sfull(s, buf), 1); mbar_init(bar_pready(s, buf), 4); mbar_init(bar_pvdone(s, buf), 1);
+      }
+    }
+    fence_mbar_init();
+  }
+  if (warp == 10) {
+    if (lane == 0) {
+      tma_prefetch_desc(&tm64); tma_prefetch_desc(&tr64);
+      if constexpr (HD == 80) { tma_prefetch_desc(&tm16); tma_prefetch_desc(&tr16); }
+    }
+    __syncwarp();
+    tmem_alloc<1>(tmem_slot, 512);
+    tmem_relinquish<1>();
+  }
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem_base = *tmem_slot_ptr;
+  auto S_COL = [](int g, int buf) { return (uint32_t)(128 * g + 64 * buf); };
+  auto O_COL = [](int g) { return (uint32_t)(256 + 128 * g); };
+
+  if (warp == 10) {
+    // ---------------------------------------------------------------------------------------- TMA producer
+    if (lane == 0) {
+      auto load_tile = [&](uint32_t dst, const CUtensorMap* m64, const CUtensorMap* m16, uint32_t bar, int col, int row) {
+        tma_load_2d(dst, m64, bar, col, row);
+        if constexpr (HD == 80) tma_load_2d(dst + 128 * 128, m16, bar, col + 64, row);
+      };
+      mbar_arrive_expect_tx(bar_q, 2 * TILE_TX);
+      load_tile(q_tile(0), &tm64, &tm16, bar_q, col_q, row_q);
+      load_tile(q_tile(1), &tm64, &tm16, bar_q, col_q, row_q + 128);
+      mbar_arrive_expect_tx(bar_rel, 2 * TILE_TX);
+      load_tile(k_tile(0), &tr64, &tr16, bar_rel, 0, 0);     // rel_pos_h rows
+      load_tile(k_tile(1), &tr64, &tr16, bar_rel, 0, 128);   // rel_pos_w rows
+      for (int s = 0; s < 2; ++s) {
+        mbar_arrive_expect_tx(bar_vfull(s), TILE_TX);
+        load_tile(v_tile(s), &tm64, &tm16, bar_vfull(s), col_v, b * 4096 + s * 128);
+      }
+      mbar_wait(bar_tdone, 0);  // the T MMAs have read the rel tables: the K ring is free
+      for (int j = 0; j < NT; ++j) {
+        const int s = j & 1;
+        const uint32_t par = (uint32_t)(((j >> 1) & 1) ^ 1);
+        if (j >= 2) mbar_wait(bar_kempty(s), par);
+        mbar_arrive_expect_tx(bar_kfull(s), TILE_TX);
+        load_tile(k_tile(s), &tm64, &tm16, bar_kfull(s), col_k, b * 4096 + j * 128);
+        if (j >= 2) {
+          mbar_wait(bar_vempty(s), par);
+          mbar_arrive_expect_tx(bar_vfull(s), TILE_TX);
+          load_tile(v_tile(s), &tm64, &tm16, bar_vfull(s), col_v, b * 4096 + j * 128);
+        }
+      }
+    }
+    __syncwarp();
+  } else if (warp >= 8) {
+    // ---------------------------------------------------------------------------------------- MMA issuer of group g
+    if (elect_one()) {
+      const int g = warp - 8;
+      const uint32_t qa = q_tile(g), qb = q_tile(g) + 128 * 128;
+      // S(t) = Q_g . K[keys 64t .. 64t+63]^T into S buffer t & 1; K tile t >> 1 sits in ring slot (t >> 1) & 1
+      auto issue_s = [&](int t) {
+        const uint32_t kt = k_tile((t >> 1) & 1);
+        issue_qk<HD>(tmem_base + S_COL(g, t & 1), qa, qb, kt + (t & 1) * 64 * 128, kt + 128 * 128 + (t & 1) * 64 * 32, IDESC_S);
+      };
+      mbar_wait(bar_q, 0);
+      mbar_wait(bar_rel, 0);
+      tc_fence_after();
+      // T_h -> columns 256g, T_w -> columns 256g + 128
+      issue_qk<HD>(tmem_base + 256 * g, qa, qb, k_tile(0), k_tile(0) + 128 * 128, IDESC_T);
+      issue_qk<HD>(tmem_base + 256 * g + 128, qa, qb, k_tile(1), k_tile(1) + 128 * 128, IDESC_T);
+      umma_commit<1>(bar_tdone);
+      mbar_wait(bar_tread, 0);  // both groups have pulled their bias terms out of TMEM (T_B overlaps O_A)
+      tc_fence_after();
+      mbar_wait(bar_kfull(0), 0);
+      tc_fence_after();
+      for (int t = 0; t < 2; ++t) {
+        issue_s(t);
+        umma_commit<1>(bar_sfull(g, t));
+      }
+      umma_commit<1>(bar_kempty(0));
+      for (int t = 0; t < NS; ++t) {
+        const int j = t >> 1, buf = t & 1, vs = j & 1;
+        const uint32_t par = (uint32_t)((t >> 1) & 1);
+        if (buf == 0) {
+          mbar_wait(bar_vfull(vs), (uint32_t)((j >> 1) & 1));
+          if (j + 1 < NT) mbar_wait(bar_kfull((j + 1) & 1), (uint32_t)(((j + 1) >> 1) & 1));
+        }
+        mbar_wait(bar_pready(g, buf), par);
+        tc_fence_after();
+        const uint32_t vt = v_tile(vs);
+        issue_pv<HD, 4>(tmem_base + O_COL(g), tmem_base + S_COL(g, buf), vt + buf * 64 * 128, vt + 128 * 128 + buf * 64 * 32,
+                        t != 0);
+        umma_commit<1>(bar_pvdone(g, buf));
+        if (t + 2 < NS) {
+          issue_s(t + 2);  // executes after the PV above (in order), the last reader of P(t) in this S buffer
+          umma_commit<1>(bar_sfull(g, buf));
+        }
+        if (buf == 1) {
+          umma_commit<1>(bar_vempty(vs));
+          if (j + 1 < NT) umma_commit<1>(bar_kempty((j + 1) & 1));
+        }
+      }
+    }
+    __syncwarp();
+  } else {
+    // ---------------------------------------------------------------------------------------- softmax groups
+    const int g = warp >> 2;          // 0: tile A, 1: tile B
+    const int r = tid & 127;          // row inside the tile == TMEM lane
+    const uint32_t lane_base = tmem_base + ((uint32_t)((warp & 3) * 32) << 16);
+    const int qt = 2 * qp + g;
+    const int qw = r & 63;
+    const int qh = 2 * qt + (r >> 6);  // warp-uniform
+    float* bh_row = biasH + (size_t)(g * 128 + r) * L::BH_PITCH;
+
+    mbar_wait(bar_tdone, 0);
+    tc_fence_after();
+    float bW[64];  // bias_w[kw] * log2e for this query
+    {
+      float t[128];  // T_w row; indexed per thread below -> lives in local memory
+      uint32_t v[32];
+#pragma unroll
+      for (int c = 0; c < 4; ++c) {
+        tmem_ld_32x32(lane_base + 256 * g + 128 + c * 32, v);
+        tmem_ld_wait();
+#pragma unroll
+        for (int i = 0; i < 32; ++i) t[c * 32 + i] = __uint_as_float(v[i]);
+      }
+      const float* tp = t + qw + 63;
+#pragma unroll
+      for (int i = 0; i < 64; ++i) bW[i] = tp[-i] * kLog2e;  // T_w[q][qw - kw + 63]
+      // T_h[q][qh - kh + 63]: qh is uniform over the warp, so the 64 needed columns start at column qh for all lanes
+      uint32_t h0[32], h1[32];
+      tmem_ld_32x32(lane_base + 256 * g + (uint32_t)qh, h0);
+      tmem_ld_32x32(lane_base + 256 * g + (uint32_t)qh + 32, h1);
+      tmem_ld_wait();
+#pragma unroll
+      for (int i = 0; i < 32; ++i) {
+        bh_row[63 - i] = __uint_as_float(h0[i]) * kLog2e;
+        bh_row[31 - i] = __uint_as_float(h1[i]) * kLog2e;
+      }
+    }
+    tc_fence_before();
+    __syncwarp();
+    if (lane == 0) mbar_arrive(bar_tread);
+
+    float m_used = 0.f, l = 0.f;
+    const float c1 = a.c1;
+    const uint32_t o_addr = lane_base + O_COL(g);
+#pragma unroll 1
+    for (int t = 0; t < NS; ++t) {
+      const int buf = t & 1;
+      const uint32_t par = (uint32_t)((t >> 1) & 1);
+      const uint32_t s_addr = lane_base + S_COL(g, buf);
+      const float bh = bh_row[t];  // key row kh = t
+      mbar_wait(bar_sfull(g, buf), par);
+      tc_fence_after();
+      uint32_t v0[32], v1[32];
+      tmem_ld_32x32(s_addr, v0);
+      tmem_ld_32x32(s_addr + 32, v1);
+      tmem_ld_wait();
+      if (t == 0) {  // shift = max over the first 32 keys
+        float mx = -INFINITY;
+#pragma unroll
+        for (int i = 0; i < 32; ++i) mx = fmaxf(mx, fmaf(__uint_as_float(v0[i]), c1, bW[i] + bh));
+        m_used = mx;
+      }
+      const float bb = bh - m_used;
+      float tmax = -INFINITY;
+      uint32_t pk[32];
+#pragma unroll
+      for (int i = 0; i < 32; i += 2) {
+        const float x0 = fmaf(__uint_as_float(v0[i]), c1, bW[i] + bb);
+        const float x1 = fmaf(__uint_as_float(v0[i + 1]), c1, bW[i + 1] + bb);
+        tmax = fmaxf(tmax, fmaxf(x0, x1));
+        const float p0 = ex2_approx(fminf(x0, 120.f)), p1 = ex2_approx(fminf(x1, 120.f));
+        l += p0 + p1;
+        pk[i >> 1] = pack_bf16x2(p0, p1);
+      }
+#pragma unroll
+      for (int i = 0; i < 32; i += 2) {
+        const float x0 = fmaf(__uint_as_float(v1[i]), c1, bW[32 + i] + bb);
+        const float x1 = fmaf(__uint_as_float(v1[i + 1]), c1, bW[32 + i + 1] + bb);
+        tmax = fmaxf(tmax, fmaxf(x0, x1));
+        const float p0 = ex2_approx(fminf(x0, 120.f)), p1 = ex2_approx(fminf(x1, 120.f));
+        l += p0 + p1;
+        pk[16 + (i >> 1)] = pack_bf16x2(p0, p1);
+      }
+      tmem_st_32x32(s_addr, pk);  // P(t) over the first 32 columns of S(t), all of which have been read
+      tmem_st_wait();
+      tc_fence_before();
+      __syncwarp();
+      if (lane == 0) mbar_arrive(bar_pready(g, buf));
+      const bool need = tmax > 32.f;
+      if (__any_sync(0xffffffffu, need)) {  // exact but cold: move the shift up and rescale the accumulator
+        mbar_wait(bar_pvdone(g, buf), par);  // PV(t) has been accumulated with the old shift
+        tc_fence_after();
+        const float alpha = need ? ex2_approx(-tmax) : 1.f;
+        if (need) m_used += tmax;
+        l *= alpha;
+        uint32_t v[16];
+#pragma unroll
+        for (int c = 0; c < HD / 16; ++c) {
+          tmem_ld_32x16(o_addr + c * 16, v);
+          tmem_ld_wait();
+#pragma unroll
+          for (int i = 0; i < 16; ++i) v[i] = __float_as_uint(__uint_as_float(v[i]) * alpha);
+          tmem_st_32x16(o_addr + c * 16, v);
+        }
+        tmem_st_wait();
+        tc_fence_before();
+      }
+    }
+    mbar_wait(bar_pvdone(g, 1), 1u);  // PV of sub-tile 63 (the 32nd completion on buffer 1)
+    tc_fence_after();
+    store_o_row<HD>(o_addr, 1.f / l, a.out + (size_t)(row_q + g * 128 + r) * a.D + col_q, true);
+  }
+
+  tc_fence_before();
+  __syncthreads();
+  if (warp == 10) tmem_dealloc<1>(tmem_base, 512);
+}
+
+}  // namespace inksam

@@ -1,6 +1,7 @@
 // Host side of the encoder attention kernels: tensor maps over the qkv matrix and the rel-pos table, launch.
 #include "common.h"
 #include "attn_tc.cuh"
+#include "attn_global2.cuh"
 
 namespace inksam {
 
@@ -16,14 +17,14 @@ static int launch_global(const __nv_bfloat16* qkv, const __nv_bfloat16* rel, con
   } else {
     tm16 = tm64; tr16 = tr64;
   }
-  constexpr int SMEM = 3 * AttnTile<HD>::bytes(128) + 128 * 66 * 4 + 64 + 1024;
-  auto kern = attn_global_kernel<HD>;
+  using L = AttnGlobal2<HD>;
+  auto kern = attn_global2_kernel<HD>;
   static bool attr_done = false;
   if (!attr_done) {
-    CUDA_TRY(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM));
+    CUDA_TRY(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, L::SMEM_BYTES));
     attr_done = true;
   }
-  kern<<<a.B * a.heads * 32, 128, SMEM, st>>>(tm64, tm16, tr64, tr16, a);
+  kern<<<a.B * a.heads * 16, L::THREADS, L::SMEM_BYTES, st>>>(tm64, tm16, tr64, tr16, a);
   CUDA_TRY(cudaGetLastError());
   return 0;
 }
