@@ -2,6 +2,7 @@
 #include "common.h"
 #include "attn_tc.cuh"
 #include "attn_global2.cuh"
+#include "attn_window2.cuh"
 
 namespace inksam {
 
@@ -43,16 +44,20 @@ static int launch_window(const __nv_bfloat16* qkv, const __nv_bfloat16* rel, con
   } else {
     tq16 = tq64; tk16 = tk64; tr16 = tr64;
   }
-  constexpr int KT = AttnTile<HD>::bytes(208);
-  constexpr int VBUF = KT > 33280 ? KT : 33792;
-  constexpr int SMEM = AttnTile<HD>::bytes(128) + KT + VBUF + 64 + 1024;
-  auto kern = attn_window_kernel<HD>;
+  using L = AttnWindow2<HD>;
+  auto kern = attn_window2_kernel<HD>;
   static bool attr_done = false;
+  static int num_sms = 0;
   if (!attr_done) {
-    CUDA_TRY(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM));
+    CUDA_TRY(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, L::SMEM_BYTES));
+    int dev = 0;
+    CUDA_TRY(cudaGetDevice(&dev));
+    CUDA_TRY(cudaDeviceGetAttribute(&num_sms, cudaDevAttrMultiProcessorCount, dev));
     attr_done = true;
   }
-  kern<<<a.B * 25 * a.heads * 2, 128, SMEM, st>>>(tq64, tq16, tk64, tk16, tr64, tr16, a);
+  const int items = a.B * 25 * a.heads * 2;
+  const int grid = items < 2 * num_sms ? items : 2 * num_sms;  // persistent: 2 CTAs per SM
+  kern<<<grid, L::THREADS, L::SMEM_BYTES, st>>>(tq64, tq16, tk64, tk16, tr64, tr16, a, items);
   CUDA_TRY(cudaGetLastError());
   return 0;
 }
