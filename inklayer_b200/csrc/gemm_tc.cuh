@@ -113,7 +113,7 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
 
   if (warp == 0) {
     // ------------------------------------------------------------ TMA producer
-    if (lane == 0) {
+    if (elect_one()) {  // elect (not lane == 0): the compiler then emits straight-line uniform-datapath code
       int stage = 0;
       uint32_t phase = 0;
       for (int tile = cluster_id; tile < num_tiles; tile += num_clusters) {
@@ -158,7 +158,7 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
     __syncwarp();
   } else if (warp == 1) {
     // ------------------------------------------------------------ MMA issuer (pair leader only)
-    if (lane == 0 && leader) {
+    if (leader && elect_one()) {
       int stage = 0;
       uint32_t phase = 0;
       int as = 0;
