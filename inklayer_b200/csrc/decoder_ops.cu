@@ -260,13 +260,14 @@ __global__ void __launch_bounds__(256) decoder_t2i_kernel(const float* __restric
                                                           long long box_stride, int ld, const int* __restrict__ box_img,
                                                           float* __restrict__ out) {
   const int box = blockIdx.x >> 3, h = blockIdx.x & 7, tid = threadIdx.x;
-  __shared__ float qs[NT][16];
+  __shared__ __align__(16) float qs[NT][16];
   __shared__ float red_m[8][NT];
   __shared__ float red[8][NT * 17];
   if (tid < NT * 16)  // 1/sqrt(16) and log2(e) folded into q
     qs[tid / 16][tid % 16] = q[(size_t)box * NT * 128 + (tid / 16) * 128 + h * 16 + tid % 16] * (0.25f * 1.4426950408889634f);
   __syncthreads();
   const float* base = kv + (size_t)(box_img ? box_img[box] : box) * box_stride + h * 16;
+  const uint32_t qs_addr = (uint32_t)__cvta_generic_to_shared(&qs[0][0]);
   float m[NT], l[NT], acc[NT][16];
 #pragma unroll
   for (int t = 0; t < NT; ++t) {
@@ -274,27 +275,52 @@ __global__ void __launch_bounds__(256) decoder_t2i_kernel(const float* __restric
 #pragma unroll
     for (int d = 0; d < 16; ++d) acc[t][d] = 0.f;
   }
+  // Each thread walks 16 keys (stride 256) with the next key's k / v rows already in flight.  The softmax shift of a
+  // token is lazy: it is set by the first key and moves (with an exact rescale of l and acc) only when a later score
+  // exceeds it by more than 2^24, so the common path is one exp2 and 17 FMAs per (token, key).
+  float4 nk[4], nv[4];
+  {
+    const float4* kr = reinterpret_cast<const float4*>(base + (size_t)tid * ld);
+#pragma unroll
+    for (int i = 0; i < 4; ++i) { nk[i] = kr[i]; nv[i] = kr[32 + i]; }
+  }
+#pragma unroll 1
   for (int j = tid; j < 4096; j += 256) {
-    const float4* kr = reinterpret_cast<const float4*>(base + (size_t)j * ld);
-    const float4* vr = reinterpret_cast<const float4*>(base + (size_t)j * ld + 128);
     float kk[16], vv[16];
 #pragma unroll
     for (int i = 0; i < 4; ++i) {
-      const float4 a = kr[i], b = vr[i];
-      kk[4 * i] = a.x; kk[4 * i + 1] = a.y; kk[4 * i + 2] = a.z; kk[4 * i + 3] = a.w;
-      vv[4 * i] = b.x; vv[4 * i + 1] = b.y; vv[4 * i + 2] = b.z; vv[4 * i + 3] = b.w;
+      kk[4 * i] = nk[i].x; kk[4 * i + 1] = nk[i].y; kk[4 * i + 2] = nk[i].z; kk[4 * i + 3] = nk[i].w;
+      vv[4 * i] = nv[i].x; vv[4 * i + 1] = nv[i].y; vv[4 * i + 2] = nv[i].z; vv[4 * i + 3] = nv[i].w;
+    }
+    if (j + 256 < 4096) {
+      const float4* kr = reinterpret_cast<const float4*>(base + (size_t)(j + 256) * ld);
+#pragma unroll
+      for (int i = 0; i < 4; ++i) { nk[i] = kr[i]; nv[i] = kr[32 + i]; }
     }
 #pragma unroll
     for (int t = 0; t < NT; ++t) {
       float sc = 0.f;
 #pragma unroll
-      for (int d = 0; d < 16; ++d) sc += qs[t][d] * kk[d];
-      const float mn = fmaxf(m[t], sc);
-      const float corr = exp2f(m[t] - mn), p = exp2f(sc - mn);
-      m[t] = mn;
-      l[t] = l[t] * corr + p;
+      for (int i = 0; i < 4; ++i) {
+        // q stays in shared memory (broadcast LDS.128, re-read per key): hoisted into registers it would be 112
+        // more live values on top of the 112 accumulators
+        float4 q4;
+        asm volatile("ld.shared.v4.f32 {%0, %1, %2, %3}, [%4];"
+                     : "=f"(q4.x), "=f"(q4.y), "=f"(q4.z), "=f"(q4.w)
+                     : "r"(qs_addr + (uint32_t)((t * 16 + 4 * i) * 4)));
+        sc += q4.x * kk[4 * i] + q4.y * kk[4 * i + 1] + q4.z * kk[4 * i + 2] + q4.w * kk[4 * i + 3];
+      }
+      if (sc > m[t] + 24.f) {  // first key (m = -inf) or a much larger score: move the shift
+        const float corr = exp2f(m[t] - sc);  // 0 for the first key
+        m[t] = sc;
+        l[t] *= corr;
 #pragma unroll
-      for (int d = 0; d < 16; ++d) acc[t][d] = acc[t][d] * corr + p * vv[d];
+        for (int d = 0; d < 16; ++d) acc[t][d] *= corr;
+      }
+      const float p = exp2f(sc - m[t]);
+      l[t] += p;
+#pragma unroll
+      for (int d = 0; d < 16; ++d) acc[t][d] += p * vv[d];
     }
   }
   // merge the 256 partial softmaxes: block max, rescale, block sum
@@ -354,51 +380,67 @@ __global__ void __launch_bounds__(256) decoder_i2t_kernel(const float* __restric
                                                           const int* __restrict__ box_img, const float* __restrict__ kv,
                                                           float* __restrict__ out) {
   const int box = blockIdx.y, tid = threadIdx.x;
-  __shared__ float ks[NT * 128], vs[NT * 128];
+  // k / v of the 7 tokens, head rows padded 16 -> 20 floats: the 8 lanes of a quarter warp (8 heads of one pixel) then
+  // read 8 disjoint 4-bank groups with one LDS.128 each (conflict-free; an unpadded row is a 4-way conflict)
+  constexpr int HP = 20;
+  __shared__ __align__(16) float ks[NT * 8 * HP], vs[NT * 8 * HP];
   for (int i = tid; i < NT * 128; i += 256) {
-    ks[i] = kv[(size_t)box * 2 * NT * 128 + i];
-    vs[i] = kv[(size_t)box * 2 * NT * 128 + NT * 128 + i];
+    const int t = i >> 7, c = i & 127;
+    ks[(t * 8 + (c >> 4)) * HP + (c & 15)] = kv[(size_t)box * 2 * NT * 128 + i];
+    vs[(t * 8 + (c >> 4)) * HP + (c & 15)] = kv[(size_t)box * 2 * NT * 128 + NT * 128 + i];
   }
   __syncthreads();
-  const int pix = blockIdx.x * 32 + (tid >> 3), h = tid & 7;
-  const float4* qr = reinterpret_cast<const float4*>(qsrc + (size_t)(box_img ? box_img[box] : box) * box_stride +
-                                                     (size_t)pix * ld + qcol + h * 16);
-  float qv[16];
+  const int h = tid & 7;
+#pragma unroll 1
+  for (int rep = 0; rep < 4; ++rep) {  // 4 x 32 pixels per block
+    const int pix = blockIdx.x * 128 + rep * 32 + (tid >> 3);
+    const float4* qr = reinterpret_cast<const float4*>(qsrc + (size_t)(box_img ? box_img[box] : box) * box_stride +
+                                                       (size_t)pix * ld + qcol + h * 16);
+    float qv[16];
 #pragma unroll
-  for (int i = 0; i < 4; ++i) {
-    const float4 a = qr[i];
-    qv[4 * i] = a.x; qv[4 * i + 1] = a.y; qv[4 * i + 2] = a.z; qv[4 * i + 3] = a.w;
+    for (int i = 0; i < 4; ++i) {
+      const float4 a = qr[i];
+      qv[4 * i] = a.x; qv[4 * i + 1] = a.y; qv[4 * i + 2] = a.z; qv[4 * i + 3] = a.w;
+    }
+    float sc[NT], mx = -INFINITY;
+#pragma unroll
+    for (int t = 0; t < NT; ++t) {
+      const float4* kr = reinterpret_cast<const float4*>(ks + (t * 8 + h) * HP);
+      float s = 0.f;
+#pragma unroll
+      for (int i = 0; i < 4; ++i) {
+        const float4 k4 = kr[i];
+        s += qv[4 * i] * k4.x + qv[4 * i + 1] * k4.y + qv[4 * i + 2] * k4.z + qv[4 * i + 3] * k4.w;
+      }
+      sc[t] = s * 0.25f;
+      mx = fmaxf(mx, sc[t]);
+    }
+    float sum = 0.f;
+#pragma unroll
+    for (int t = 0; t < NT; ++t) { sc[t] = expf(sc[t] - mx); sum += sc[t]; }
+    const float inv = 1.f / sum;
+    float o[16];
+#pragma unroll
+    for (int d = 0; d < 16; ++d) o[d] = 0.f;
+#pragma unroll
+    for (int t = 0; t < NT; ++t) {
+      const float p = sc[t] * inv;
+      const float4* vr = reinterpret_cast<const float4*>(vs + (t * 8 + h) * HP);
+#pragma unroll
+      for (int i = 0; i < 4; ++i) {
+        const float4 v4 = vr[i];
+        o[4 * i] += p * v4.x; o[4 * i + 1] += p * v4.y; o[4 * i + 2] += p * v4.z; o[4 * i + 3] += p * v4.w;
+      }
+    }
+    float4* dst = reinterpret_cast<float4*>(out + ((size_t)box * 4096 + pix) * 128 + h * 16);
+#pragma unroll
+    for (int i = 0; i < 4; ++i) dst[i] = make_float4(o[4 * i], o[4 * i + 1], o[4 * i + 2], o[4 * i + 3]);
   }
-  float sc[NT], mx = -INFINITY;
-#pragma unroll
-  for (int t = 0; t < NT; ++t) {
-    float s = 0.f;
-#pragma unroll
-    for (int d = 0; d < 16; ++d) s += qv[d] * ks[t * 128 + h * 16 + d];
-    sc[t] = s * 0.25f;
-    mx = fmaxf(mx, sc[t]);
-  }
-  float sum = 0.f;
-#pragma unroll
-  for (int t = 0; t < NT; ++t) { sc[t] = expf(sc[t] - mx); sum += sc[t]; }
-  const float inv = 1.f / sum;
-  float o[16];
-#pragma unroll
-  for (int d = 0; d < 16; ++d) o[d] = 0.f;
-#pragma unroll
-  for (int t = 0; t < NT; ++t) {
-    const float p = sc[t] * inv;
-#pragma unroll
-    for (int d = 0; d < 16; ++d) o[d] += p * vs[t * 128 + h * 16 + d];
-  }
-  float4* dst = reinterpret_cast<float4*>(out + ((size_t)box * 4096 + pix) * 128 + h * 16);
-#pragma unroll
-  for (int i = 0; i < 4; ++i) dst[i] = make_float4(o[4 * i], o[4 * i + 1], o[4 * i + 2], o[4 * i + 3]);
 }
 
 int launch_decoder_i2t(const float* qsrc, long long box_stride, int ld, int qcol, const int* box_img, const float* kv,
                        float* out, int boxes, cudaStream_t st) {
-  decoder_i2t_kernel<<<dim3(128, boxes), 256, 0, st>>>(qsrc, box_stride, ld, qcol, box_img, kv, out);
+  decoder_i2t_kernel<<<dim3(32, boxes), 256, 0, st>>>(qsrc, box_stride, ld, qcol, box_img, kv, out);
   CUDA_TRY(cudaGetLastError());
   return 0;
 }
