@@ -40,10 +40,11 @@ __device__ __forceinline__ float gelu_erf(float x) {
   return fmaf(fabsf(hx), erf_abs, hx);
 }
 
-// epilogue warps per CTA: 8 (two per TMEM lane quarter, splitting the columns) except for the epilogues that
-// need whole-row LayerNorm statistics, which keep one warp per lane quarter
+// epilogue warps per CTA: 8 (two per TMEM lane quarter, splitting the columns) except for the encoder-neck epilogues
+// with whole-row LayerNorm statistics, which keep one warp per lane quarter (EPI_RESID_LN_F32 splits the row and
+// exchanges the partial statistics through shared memory)
 __host__ __device__ constexpr int gemm_epi_warps(int epi) {
-  return (epi == EPI_LN_BF16_PAD || epi == EPI_LN_F32_NCHW || epi == EPI_RESID_LN_F32) ? 4 : 8;
+  return (epi == EPI_LN_BF16_PAD || epi == EPI_LN_F32_NCHW) ? 4 : 8;
 }
 
 template <int CG, int TF32, int BN>
@@ -55,7 +56,7 @@ struct GemmCfg {
   static constexpr int STAGE_BYTES = A_BYTES + B_BYTES;
   static constexpr int STAGES = (192 * 1024) / STAGE_BYTES > 8 ? 8 : (192 * 1024) / STAGE_BYTES;
   static constexpr int KELEMS = TF32 ? 32 : 64;  // elements per 128-byte smem row
-  static constexpr int SMEM_BYTES = STAGES * STAGE_BYTES + 1024 /*align slack*/ + 256 /*barriers*/;
+  static constexpr int SMEM_BYTES = STAGES * STAGE_BYTES + 1024 /*align slack*/ + 256 /*barriers*/ + 4096 /*LN partials*/;
   static constexpr uint32_t IDESC = make_idesc(TF32 ? 2u : 1u, BM * CG, BN);
   static constexpr int TMEM_COLS = 2 * BN;       // double-buffered accumulators (power of two: 256 or 512)
 };
@@ -284,7 +285,72 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
             }
           }
         }
-      } else if constexpr (EPI == EPI_LN_BF16_PAD || EPI == EPI_LN_F32_NCHW || EPI == EPI_RESID_LN_F32) {
+      } else if constexpr (EPI == EPI_RESID_LN_F32) {
+        // out = LayerNorm_N(resid + acc + bias), N == BN: the two warps of a lane quarter take half a row each.
+        // Pass 1 adds residual (prefetched a chunk ahead) and bias, keeps the sums in TMEM and accumulates sum and sum
+        // of squares; the halves meet through shared memory (one named barrier per lane quarter); pass 2 normalises.
+        uint32_t v[32];
+        float* f = reinterpret_cast<float*>(v);
+        uint32_t rr[2][32];
+        int mm = row_ok ? (g.resid_mod ? m % g.resid_mod : m) : 0;
+        if (g.row_img != nullptr && row_ok) mm += __ldg(g.row_img + m / g.resid_mod) * g.resid_mod;
+        const float* rrow = g.resid + (size_t)mm * g.ldo;
+#pragma unroll
+        for (int h = 0; h < 4; ++h) ld_global_v8(rrow + c_first * 32 + h * 8, *reinterpret_cast<uint32_t(*)[8]>(&rr[0][h * 8]));
+        float sum = 0.f, sq = 0.f;
+#pragma unroll
+        for (int ci = 0; ci < NCW; ++ci) {
+          const int c = c_first + ci;
+          tmem_ld_32x32(taddr + c * 32, v);
+          if (ci + 1 < NCW) {
+#pragma unroll
+            for (int h = 0; h < 4; ++h)
+              ld_global_v8(rrow + (c + 1) * 32 + h * 8, *reinterpret_cast<uint32_t(*)[8]>(&rr[(ci + 1) & 1][h * 8]));
+          }
+          tmem_ld_wait();
+#pragma unroll
+          for (int j = 0; j < 32; j += 4) {
+            const float4 b4 = __ldg(reinterpret_cast<const float4*>(g.bias + c * 32 + j));
+            f[j] += b4.x + __uint_as_float(rr[ci & 1][j]);
+            f[j + 1] += b4.y + __uint_as_float(rr[ci & 1][j + 1]);
+            f[j + 2] += b4.z + __uint_as_float(rr[ci & 1][j + 2]);
+            f[j + 3] += b4.w + __uint_as_float(rr[ci & 1][j + 3]);
+          }
+          tmem_st_32x32(taddr + c * 32, v);
+#pragma unroll
+          for (int j = 0; j < 32; ++j) { sum += f[j]; sq += f[j] * f[j]; }
+        }
+        tmem_st_wait();
+        float2* part = reinterpret_cast<float2*>(smem_raw + (bar_base - smem_u32(smem_raw)) + 256) + as * 256;
+        part[half * 128 + q * 32 + lane] = make_float2(sum, sq);
+        asm volatile("bar.sync %0, 64;" ::"r"(1 + q) : "memory");
+        const float2 other = part[(half ^ 1) * 128 + q * 32 + lane];
+        const float mean = (sum + other.x) * (1.0f / BN);
+        const float var = fmaxf((sq + other.y) * (1.0f / BN) - mean * mean, 0.f);
+        const float rstd = rsqrtf(var + g.ln_eps);
+#pragma unroll
+        for (int ci = 0; ci < NCW; ++ci) {
+          const int c = c_first + ci;
+          tmem_ld_32x32(taddr + c * 32, v);
+          tmem_ld_wait();
+          if (row_ok) {
+            float* o = reinterpret_cast<float*>(g.out) + (size_t)m * g.ldo + c * 32;
+#pragma unroll
+            for (int h = 0; h < 4; ++h) {
+              uint32_t pk[8];
+              const float4 w0 = __ldg(reinterpret_cast<const float4*>(g.ln_w + c * 32 + h * 8));
+              const float4 w1 = __ldg(reinterpret_cast<const float4*>(g.ln_w + c * 32 + h * 8 + 4));
+              const float4 b0 = __ldg(reinterpret_cast<const float4*>(g.ln_b + c * 32 + h * 8));
+              const float4 b1 = __ldg(reinterpret_cast<const float4*>(g.ln_b + c * 32 + h * 8 + 4));
+              const float ww[8] = {w0.x, w0.y, w0.z, w0.w, w1.x, w1.y, w1.z, w1.w};
+              const float bb[8] = {b0.x, b0.y, b0.z, b0.w, b1.x, b1.y, b1.z, b1.w};
+#pragma unroll
+              for (int j = 0; j < 8; ++j) pk[j] = __float_as_uint((f[h * 8 + j] - mean) * rstd * ww[j] + bb[j]);
+              st_global_v8(o + h * 8, pk);
+            }
+          }
+        }
+      } else if constexpr (EPI == EPI_LN_BF16_PAD || EPI == EPI_LN_F32_NCHW) {
         // LayerNorm over the N == BN columns of this thread's row; the row lives in TMEM, so the three
         // passes (mean, variance, normalise) re-read TMEM instead of holding 256 registers.
         uint32_t v[32];
