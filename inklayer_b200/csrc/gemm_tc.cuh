@@ -56,7 +56,7 @@ struct GemmCfg {
   static constexpr int STAGE_BYTES = A_BYTES + B_BYTES;
   static constexpr int STAGES = (192 * 1024) / STAGE_BYTES > 8 ? 8 : (192 * 1024) / STAGE_BYTES;
   static constexpr int KELEMS = TF32 ? 32 : 64;  // elements per 128-byte smem row
-  static constexpr int SMEM_BYTES = STAGES * STAGE_BYTES + 1024 /*align slack*/ + 256 /*barriers*/ + 4096 /*LN partials*/;
+  static constexpr int SMEM_BYTES = STAGES * STAGE_BYTES + 1024 /*align slack*/ + 256 /*barriers*/ + 4096 /*LN partials*/ + 1024 /*epilogue constants*/;
   static constexpr uint32_t IDESC = make_idesc(TF32 ? 2u : 1u, BM * CG, BN);
   static constexpr int TMEM_COLS = 2 * BN;       // double-buffered accumulators (power of two: 256 or 512)
 };
@@ -106,6 +106,16 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
   if (warp == 2) {
     tmem_alloc<CG>(tmem_slot, C::TMEM_COLS);
     tmem_relinquish<CG>();
+  }
+  // per-channel constants of the conv-transpose epilogue, read back with volatile broadcast LDS.128 so that the
+  // compiler does not hoist 192 loop-invariant values into registers
+  const uint32_t econst = bar_base + 256 + 4096;
+  if constexpr (EPI == EPI_UPSCALE1) {
+    float* ec = reinterpret_cast<float*>(smem_raw + (econst - smem_u32(smem_raw)));
+    if (threadIdx.x >= 128 && threadIdx.x < 192) {
+      const int c = threadIdx.x - 128;
+      ec[c] = g.bias[c]; ec[64 + c] = g.ln_w[c]; ec[128 + c] = g.ln_b[c];
+    }
   }
   tc_fence_before();
   if constexpr (CG == 2) cluster_sync_all(); else __syncthreads();
@@ -439,12 +449,18 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
           tmem_ld_32x32(taddr + sp * 64, v[0]);
           tmem_ld_32x32(taddr + sp * 64 + 32, v[1]);
           tmem_ld_wait();
+          auto lds4 = [](uint32_t addr) {
+            float4 r;
+            asm volatile("ld.shared.v4.f32 {%0, %1, %2, %3}, [%4];" : "=f"(r.x), "=f"(r.y), "=f"(r.z), "=f"(r.w) : "r"(addr));
+            return r;
+          };
           float sum = 0.f;
 #pragma unroll
-          for (int j = 0; j < 32; ++j) {
-            f0[j] += __ldg(g.bias + j);
-            f1[j] += __ldg(g.bias + 32 + j);
-            sum += f0[j] + f1[j];
+          for (int j = 0; j < 32; j += 4) {
+            const float4 b0 = lds4(econst + 4 * j), b1 = lds4(econst + 4 * (32 + j));
+            f0[j] += b0.x; f0[j + 1] += b0.y; f0[j + 2] += b0.z; f0[j + 3] += b0.w;
+            f1[j] += b1.x; f1[j + 1] += b1.y; f1[j + 2] += b1.z; f1[j + 3] += b1.w;
+            sum += (f0[j] + f0[j + 1]) + (f0[j + 2] + f0[j + 3]) + (f1[j] + f1[j + 1]) + (f1[j + 2] + f1[j + 3]);
           }
           const float mean = sum * (1.0f / 64);
           float sq = 0.f;
@@ -455,9 +471,17 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
           }
           const float rstd = rsqrtf(sq * (1.0f / 64) + g.ln_eps);
 #pragma unroll
-          for (int j = 0; j < 32; ++j) {
-            f0[j] = gelu_erf((f0[j] - mean) * rstd * __ldg(g.ln_w + j) + __ldg(g.ln_b + j));
-            f1[j] = gelu_erf((f1[j] - mean) * rstd * __ldg(g.ln_w + 32 + j) + __ldg(g.ln_b + 32 + j));
+          for (int j = 0; j < 32; j += 4) {
+            const float4 w0 = lds4(econst + 4 * (64 + j)), w1 = lds4(econst + 4 * (96 + j));
+            const float4 c0 = lds4(econst + 4 * (128 + j)), c1 = lds4(econst + 4 * (160 + j));
+            f0[j] = gelu_erf((f0[j] - mean) * rstd * w0.x + c0.x);
+            f0[j + 1] = gelu_erf((f0[j + 1] - mean) * rstd * w0.y + c0.y);
+            f0[j + 2] = gelu_erf((f0[j + 2] - mean) * rstd * w0.z + c0.z);
+            f0[j + 3] = gelu_erf((f0[j + 3] - mean) * rstd * w0.w + c0.w);
+            f1[j] = gelu_erf((f1[j] - mean) * rstd * w1.x + c1.x);
+            f1[j + 1] = gelu_erf((f1[j + 1] - mean) * rstd * w1.y + c1.y);
+            f1[j + 2] = gelu_erf((f1[j + 2] - mean) * rstd * w1.z + c1.z);
+            f1[j + 3] = gelu_erf((f1[j + 3] - mean) * rstd * w1.w + c1.w);
           }
           if (row_ok) {
             const int Y = 2 * y + (sp >> 1), X = 2 * x + (sp & 1);
