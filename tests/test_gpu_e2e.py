@@ -168,3 +168,26 @@ def test_segment_stream_matches_predictor():
         # batch-of-2 vs batch-of-1 encoder launches are the same arithmetic per image: identical masks
         assert mask_iou(got[i], m[:, 0].cpu().numpy()).min() >= 0.9999
     assert seg.h2d_bytes > 0 and seg.d2h_bytes == sum(len(b) * s[0] * s[1] for b, s in zip(boxes, shapes))
+
+
+def test_vit_l_matches_oracle():
+    """Config 5 coverage: ViT-L (D = 1024, 24 blocks, head_dim 64, global blocks 5/11/17/23) against the CPU oracle run on
+    this box (the oracle itself is pinned to the reference by the tiny / ViT-B / ViT-H golden vectors)."""
+    from inklayer_b200.synth import synthetic_boxes, synthetic_sketch
+
+    cfg_name = "vit_l"
+    sd = synthetic_state_dict(CONFIGS[cfg_name], 2)
+    img = synthetic_sketch(5, 900, 1024)
+    boxes = torch.from_numpy(synthetic_boxes(5, 6, 900, 1024))
+    sam = build_sam_from_state_dict(sd, CONFIGS[cfg_name]).to("cuda")
+    pred = SamPredictor(sam)
+    pred.set_image(img)
+    tb = pred.transform.apply_boxes_torch(boxes, img.shape[:2])
+    masks, iou, low = pred.predict_torch(None, None, boxes=tb.cuda(), multimask_output=False)
+    ora = O.OraclePredictor(O.CONFIGS[cfg_name], sd)
+    ora.set_image(img)
+    m_ref, i_ref, l_ref = ora.predict_torch(O.apply_boxes(boxes, img.shape[:2]))
+    e, lo = rel_rms(pred.features.cpu(), ora.features), rel_rms(low.cpu(), l_ref)
+    ious = mask_iou(masks.cpu().numpy(), m_ref.numpy())
+    print(f"vit_l: emb rel-RMS {e:.2e}  low-res rel-RMS {lo:.2e}  min IoU {ious.min():.4f}")
+    assert e <= 1e-2 and lo <= 1e-2 and ious.min() >= 0.99
