@@ -37,6 +37,9 @@ SIGNATURES = {
     "inksam_profile_enable": (c_int, [c_void_p, c_int]),
     "inksam_profile_read": (c_int, [c_void_p, POINTER(ctypes.c_double), POINTER(ctypes.c_double), POINTER(c_longlong)]),
     "inksam_last_error": (c_char_p, []),
+    "inksam_morph_kernel_size": (c_int, [c_int, c_int]),
+    "inksam_clean_masks": (c_int, [c_void_p, c_int, c_int, c_int, c_int, c_void_p, POINTER(c_longlong), c_void_p]),
+    "inksam_content_iou": (c_int, [c_void_p, c_void_p, c_int, c_int, c_int, c_int, c_void_p, POINTER(c_longlong), c_void_p]),
     "inksam_op_gemm": (c_int, [c_int, c_int, c_int, c_int, c_void_p, c_int, c_void_p, c_int, c_int, c_int, c_int, c_void_p,
                                c_int, c_void_p, c_void_p, c_void_p, c_int, c_void_p, c_void_p, c_float, c_void_p, c_int,
                                c_int, c_int, c_int, c_void_p]),

@@ -18,7 +18,7 @@ from oracle import sam_oracle as O
 
 def declared_functions():
     names = []
-    for hdr in ("inksam.h", "inksam_ops.h"):
+    for hdr in ("inksam.h", "inksam_ops.h", "inksam_refine.h"):
         src = open(os.path.join(ROOT, "include", hdr)).read()
         src = re.sub(r"/\*.*?\*/", "", src, flags=re.S)
         names += re.findall(r"\b(inksam_[a-z0-9_]+)\s*\(", src)
