@@ -43,5 +43,8 @@ int launch_repack(const float* in, void* out, int out_bf16, const long long* ish
                   cudaStream_t st);
 int launch_postprocess(const float* low, unsigned char* masks, float* logits, int K, int in_h, int in_w, int H, int W,
                        float thr, cudaStream_t st);
+// boxes of several images (segments with their own geometry) in one launch; in_hw / orig_hw: [nseg][2]
+int launch_postprocess_batch(int nseg, const float* const* low, unsigned char* const* masks, float* const* logits, const int* n,
+                             const int* in_hw, const int* orig_hw, float thr, cudaStream_t st);
 
 }  // namespace inksam

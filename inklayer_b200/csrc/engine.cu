@@ -593,18 +593,31 @@ int decode_chunk(inksam_handle* h, const float* keys0, const float* kvq0, char* 
     c.g.M = n * 16384; c.g.N = 128; c.g.K = 64; c.g.ldo = 128; c.g.out = low; c.g.bias = u3b; c.g.hyper = s.hyper;
     INK_TRY(run_gemm(h, c, st));
   }
-  // ---- fused upsample + crop + resize + threshold: one launch per image that has boxes in this chunk
-  for (int i = 0; i < seg.n; ++i) {
-    const int b0 = seg.start[i] > k0 ? seg.start[i] : k0;
-    const int b1 = seg.start[i + 1] < k0 + n ? seg.start[i + 1] : k0 + n;
-    if (b1 <= b0) continue;
-    const ImgGeom& gm = geom[i];
-    const size_t HW = (size_t)gm.H * gm.W;
-    const size_t mo = gm.mask_off + (size_t)(b0 - seg.start[i]) * HW;
-    ++h->launches;
-    Prof p(h, CAT_POST, (double)(b1 - b0) * (65536.0 * 4 + (double)HW * ((masks ? 1 : 0) + (logits ? 4 : 0))), st);
-    INK_TRY(launch_postprocess(low + (size_t)(b0 - k0) * 65536, masks ? masks + mo : nullptr, logits ? logits + mo : nullptr,
-                               b1 - b0, gm.in_h, gm.in_w, gm.H, gm.W, thr, st));
+  // ---- fused upsample + crop + resize + threshold: one launch for every box of the chunk (a segment per image)
+  {
+    const float* p_low[kMaxDecodeImages]; unsigned char* p_mask[kMaxDecodeImages]; float* p_log[kMaxDecodeImages];
+    int cnt[kMaxDecodeImages], in_hw[2 * kMaxDecodeImages], orig_hw[2 * kMaxDecodeImages], ns = 0;
+    double bytes = 0;
+    for (int i = 0; i < seg.n; ++i) {
+      const int b0 = seg.start[i] > k0 ? seg.start[i] : k0;
+      const int b1 = seg.start[i + 1] < k0 + n ? seg.start[i + 1] : k0 + n;
+      if (b1 <= b0) continue;
+      const ImgGeom& gm = geom[i];
+      const size_t HW = (size_t)gm.H * gm.W;
+      const size_t mo = gm.mask_off + (size_t)(b0 - seg.start[i]) * HW;
+      p_low[ns] = low + (size_t)(b0 - k0) * 65536;
+      p_mask[ns] = masks ? masks + mo : nullptr;
+      p_log[ns] = logits ? logits + mo : nullptr;
+      cnt[ns] = b1 - b0;
+      in_hw[2 * ns] = gm.in_h; in_hw[2 * ns + 1] = gm.in_w; orig_hw[2 * ns] = gm.H; orig_hw[2 * ns + 1] = gm.W;
+      bytes += (double)(b1 - b0) * (65536.0 * 4 + (double)HW * ((masks ? 1 : 0) + (logits ? 4 : 0)));
+      ++ns;
+    }
+    if (ns > 0 && (masks || logits)) {
+      ++h->launches;
+      Prof p(h, CAT_POST, bytes, st);
+      INK_TRY(launch_postprocess_batch(ns, p_low, masks ? p_mask : nullptr, logits ? p_log : nullptr, cnt, in_hw, orig_hw, thr, st));
+    }
   }
   return 0;
 }

@@ -79,21 +79,41 @@ def test_fill_pad_rows():
 
 
 @pytest.mark.parametrize("inp,orig", [((1024, 1024), (1024, 1024)), ((819, 1024), (600, 750)), ((1024, 1024), (750, 750)),
-                                      ((1024, 577), (1333, 751))])
+                                      ((1024, 577), (1333, 751)), ((768, 1024), (768, 1024)), ((1024, 683), (1024, 683)),
+                                      ((1024, 640), (2048, 1280)), ((3, 1024), (3, 1024)), ((1024, 16), (1024, 16))])
 def test_postprocess_matches_interpolate(inp, orig):
-    """Fused two-stage bilinear + threshold vs Sam.postprocess_masks (oracle.postprocess_masks)."""
+    """Fused two-stage bilinear + threshold vs Sam.postprocess_masks (oracle.postprocess_masks): masks + logits (general
+    path), masks alone (the 4x16-patch fast path when original == input size and rows are 16-byte aligned) and masks
+    written at a misaligned base address."""
     lib = _lib.load()
     K = 3
     low = torch.randn(K, 1, 256, 256, generator=torch.Generator().manual_seed(5)) * 0.1
     ref = O.postprocess_masks(CFG, low, inp, orig)
     H, W = orig
+    d_low = low.cuda()
     masks = torch.empty(K, 1, H, W, dtype=torch.uint8, device="cuda")
     logits = torch.empty(K, 1, H, W, dtype=torch.float32, device="cuda")
-    _lib.check(lib.inksam_op_postprocess(ptr(low.cuda()), ptr(masks), ptr(logits), K, inp[0], inp[1], H, W,
+    _lib.check(lib.inksam_op_postprocess(ptr(d_low), ptr(masks), ptr(logits), K, inp[0], inp[1], H, W,
                                          ctypes.c_float(0.0), stream()))
     assert (logits.cpu() - ref).abs().max().item() < 2e-6
     m_ref = ref > 0.0
-    disagree = (masks.cpu().bool() != m_ref)
-    assert (ref[disagree].abs() < 2e-6).all()  # only where the logit is within rounding of the threshold
-    assert disagree.float().mean().item() < 1e-4
-    assert set(masks.unique().tolist()) <= {0, 1}
+
+    def check_masks(m):
+        disagree = (m.cpu().bool() != m_ref)
+        assert (ref[disagree].abs() < 2e-6).all()  # only where the logit is within rounding of the threshold
+        assert disagree.float().mean().item() < 1e-4
+        assert set(m.unique().tolist()) <= {0, 1}
+
+    check_masks(masks)
+    only = torch.full((K, 1, H, W), 7, dtype=torch.uint8, device="cuda")
+    _lib.check(lib.inksam_op_postprocess(ptr(d_low), ptr(only), None, K, inp[0], inp[1], H, W, ctypes.c_float(0.0), stream()))
+    check_masks(only)
+    diff = (only != masks).cpu()
+    assert (ref[diff].abs() < 2e-6).all()  # the two code paths may contract FMAs differently
+    buf = torch.full((K * H * W + 32,), 7, dtype=torch.uint8, device="cuda")
+    for shift in (1, 6):
+        buf.fill_(7)
+        _lib.check(lib.inksam_op_postprocess(ptr(d_low), buf.data_ptr() + shift, None, K, inp[0], inp[1], H, W,
+                                             ctypes.c_float(0.0), stream()))
+        assert torch.equal(buf[shift:shift + K * H * W].view(K, 1, H, W), masks)
+        assert (buf[:shift] == 7).all() and (buf[shift + K * H * W:] == 7).all()  # nothing written outside
