@@ -62,6 +62,15 @@ int inksam_op_fill_pad_rows(void* qkv, const float* bias, int B, int cols, void*
 int inksam_op_postprocess(const float* low, unsigned char* masks, float* logits, int K, int in_h, int in_w, int H, int W,
                           float thr, void* stream);
 
+/* ResizeLongestSide.apply_image on the device: Pillow's 8-bit bilinear resample (torchvision resize of a PIL image,
+ * SA/utils/transforms.py:26-31; algorithm of Pillow libImaging/Resample.c), bit-exact with the host path.
+ * src: uint8 [H][W][3] with src_row_pitch bytes per row; dst: uint8 [out_h][out_w][3] with dst_row_pitch bytes per row
+ * (e.g. a 1024x1024x3 container, pitch 3072); workspace: inksam_resize_workspace_bytes(H, W, out_h, out_w) device bytes
+ * owned by the caller, in use until the call's work on `stream` has finished. */
+size_t inksam_resize_workspace_bytes(int H, int W, int out_h, int out_w);
+int inksam_resize_u8(const uint8_t* src, int H, int W, long long src_row_pitch, uint8_t* dst, int out_h, int out_w,
+                     long long dst_row_pitch, void* workspace, void* stream);
+
 const char* inksam_last_error(void);
 
 #ifdef __cplusplus

@@ -6,7 +6,7 @@ from __future__ import annotations
 
 import ctypes
 import os
-from ctypes import POINTER, c_char_p, c_float, c_int, c_int64, c_longlong, c_void_p
+from ctypes import POINTER, c_char_p, c_float, c_int, c_int64, c_longlong, c_size_t, c_void_p
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
 LIB_PATH = os.path.join(_HERE, "libinksam.so")
@@ -49,6 +49,8 @@ SIGNATURES = {
                                    POINTER(c_float), POINTER(c_float), c_void_p, c_void_p]),
     "inksam_op_fill_pad_rows": (c_int, [c_void_p, c_void_p, c_int, c_int, c_void_p]),
     "inksam_op_postprocess": (c_int, [c_void_p, c_void_p, c_void_p, c_int, c_int, c_int, c_int, c_int, c_float, c_void_p]),
+    "inksam_resize_workspace_bytes": (c_size_t, [c_int, c_int, c_int, c_int]),
+    "inksam_resize_u8": (c_int, [c_void_p, c_int, c_int, c_longlong, c_void_p, c_int, c_int, c_longlong, c_void_p, c_void_p]),
 }
 
 _lib = None

@@ -56,7 +56,8 @@ static int launch_window(const __nv_bfloat16* qkv, const __nv_bfloat16* rel, con
     attr_done = true;
   }
   const int items = a.B * 25 * a.heads * 2;
-  const int grid = items < 2 * num_sms ? items : 2 * num_sms;  // persistent: 2 CTAs per SM
+  const int pairs = items / 2;  // a CTA takes both row tiles of a (window, head) so that K and V are loaded once
+  const int grid = pairs < 2 * num_sms ? pairs : 2 * num_sms;  // persistent: 2 CTAs per SM
   kern<<<grid, L::THREADS, L::SMEM_BYTES, st>>>(tq64, tq16, tk64, tk16, tr64, tr16, a, items);
   CUDA_TRY(cudaGetLastError());
   return 0;

@@ -100,6 +100,35 @@ __device__ __forceinline__ void store_o_row(uint32_t o_taddr, float inv, __nv_bf
   }
 }
 
+// Same, with every tcgen05.ld issued before a single wait (the row's HD fp32 values sit in registers at once).
+template <int HD>
+__device__ __forceinline__ void store_o_row_once(uint32_t o_taddr, float inv, __nv_bfloat16* dst, bool valid) {
+  uint32_t v0[32], v1[32], w[16];
+  tmem_ld_32x32(o_taddr, v0);
+  tmem_ld_32x32(o_taddr + 32, v1);
+  if constexpr (HD == 80) tmem_ld_32x16(o_taddr + 64, w);
+  tmem_ld_wait();
+  if (!valid) return;
+#pragma unroll
+  for (int c = 0; c < 2; ++c) {
+    const uint32_t (&v)[32] = c ? v1 : v0;
+#pragma unroll
+    for (int h = 0; h < 2; ++h) {
+      uint32_t pk[8];
+#pragma unroll
+      for (int j = 0; j < 8; ++j)
+        pk[j] = pack_bf16x2(__uint_as_float(v[h * 16 + 2 * j]) * inv, __uint_as_float(v[h * 16 + 2 * j + 1]) * inv);
+      st_global_v8(dst + c * 32 + h * 16, pk);
+    }
+  }
+  if constexpr (HD == 80) {
+    uint32_t pk[8];
+#pragma unroll
+    for (int j = 0; j < 8; ++j) pk[j] = pack_bf16x2(__uint_as_float(w[2 * j]) * inv, __uint_as_float(w[2 * j + 1]) * inv);
+    st_global_v8(dst + 64, pk);
+  }
+}
+
 // ------------------------------------------------------------------------------------------------ global
 // Tensor maps over the qkv matrix [B*4096][3D] (natural token order): tm64 box {64 cols, 128 rows} SW128,
 // tm16 box {16, 128} SW32; over the rel table [256][HD] (rows 0..126 rel_pos_h, 128..254 rel_pos_w):

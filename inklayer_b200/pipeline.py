@@ -28,8 +28,15 @@ class _Slot:
         self.dev_img = torch.empty((max_batch, S, S, 3), dtype=torch.uint8, device=sam.device)
         self.dev_masks: Optional[torch.Tensor] = None
         self.host_masks: Optional[torch.Tensor] = None
+        self.host_raw: Optional[torch.Tensor] = None   # pinned staging of sketches that still need the resize
+        self.dev_raw: Optional[torch.Tensor] = None
         self.ev_in, self.ev_done, self.ev_out = torch.cuda.Event(), torch.cuda.Event(), torch.cuda.Event()
         self.views: list = []
+
+    def raw_buffers(self, nbytes: int, device) -> None:
+        if self.host_raw is None or self.host_raw.numel() < nbytes:
+            self.host_raw = torch.empty(nbytes, dtype=torch.uint8).pin_memory()
+            self.dev_raw = torch.empty(nbytes, dtype=torch.uint8, device=device)
 
     def mask_buffers(self, nbytes: int, device) -> None:
         if self.dev_masks is None or self.dev_masks.numel() < nbytes:
@@ -66,13 +73,24 @@ class SketchSegmenter:
             raise RuntimeError(f"a batch holds 1..{self.max_batch} sketches, got {B}")
         slot = self._slots[self._next]
         self._next = (self._next + 1) % len(self._slots)
-        sizes, in_sizes = [], []
+        # sketches already in the model's input frame go straight into the pinned batch container; the others are staged
+        # as they are and resized ON THE DEVICE (Sam.resize_longest_side: bit-exact with the reference's Pillow resize)
+        sizes, in_sizes, raw = [], [], []   # raw: (slot index, byte offset, H, W)
+        raw_bytes = 0
         for i, im in enumerate(images):
-            r = self.transform.apply_image(im)  # host resize (Pillow, exact), identity at 1024x1024
-            h, w = r.shape[:2]
-            slot.host_img[i, :h, :w].copy_(torch.from_numpy(r))
-            sizes.append(tuple(int(v) for v in im.shape[:2]))
+            H, W = int(im.shape[0]), int(im.shape[1])
+            h, w = self.transform.get_preprocess_shape(H, W, self.transform.target_length)
+            sizes.append((H, W))
             in_sizes.append((h, w))
+            if (h, w) == (H, W):
+                slot.host_img[i, :h, :w].copy_(torch.from_numpy(np.ascontiguousarray(im)))
+            else:
+                raw.append((i, raw_bytes, H, W))
+                raw_bytes += (H * W * 3 + 255) // 256 * 256
+        if raw:
+            slot.raw_buffers(raw_bytes, dev)
+            for i, off, H, W in raw:
+                slot.host_raw[off:off + H * W * 3].view(H, W, 3).copy_(torch.from_numpy(np.ascontiguousarray(images[i])))
         tbs = [self.transform.apply_boxes_torch(torch.as_tensor(np.asarray(bx, dtype=np.float32).reshape(-1, 4)), sizes[i])
                for i, bx in enumerate(boxes)]
         hb = torch.cat(tbs).pin_memory() if sum(len(t) for t in tbs) else torch.zeros((0, 4))
@@ -81,12 +99,23 @@ class SketchSegmenter:
         caller = torch.cuda.current_stream(dev)
         self._s_in.wait_stream(caller)
         with torch.cuda.stream(self._s_in):
-            slot.dev_img[:B].copy_(slot.host_img[:B], non_blocking=True)
+            if len(raw) < B:
+                if not raw:
+                    slot.dev_img[:B].copy_(slot.host_img[:B], non_blocking=True)
+                else:
+                    skip = {r[0] for r in raw}
+                    for i in range(B):
+                        if i not in skip:
+                            slot.dev_img[i].copy_(slot.host_img[i], non_blocking=True)
+            if raw:
+                slot.dev_raw[:raw_bytes].copy_(slot.host_raw[:raw_bytes], non_blocking=True)
             db = hb.to(dev, non_blocking=True)
             slot.ev_in.record()
-        self.h2d_bytes += B * slot.host_img[0].numel() + hb.numel() * 4
+        self.h2d_bytes += (B - len(raw)) * slot.host_img[0].numel() + sum(H * W * 3 for _, _, H, W in raw) + hb.numel() * 4
         with torch.cuda.stream(self._s_run):
             self._s_run.wait_event(slot.ev_in)
+            for i, off, H, W in raw:
+                sam.resize_longest_side(slot.dev_raw[off:off + H * W * 3].view(H, W, 3), out=slot.dev_img[i])
             feats = sam.encode(slot.dev_img[:B], in_sizes)
             counts = [len(t) for t in tbs]
             splits = list(torch.split(db, counts)) if db.numel() else [db[:0] for _ in tbs]

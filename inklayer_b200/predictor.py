@@ -31,14 +31,15 @@ class SamPredictor:
 
     # ------------------------------------------------------------------ encode
     def set_image(self, image: np.ndarray, image_format: str = "RGB") -> None:
-        """predictor.py:34-60: uint8 HWC image -> host resize -> device -> encoder; caches the embedding."""
+        """predictor.py:34-60: uint8 HWC image -> device -> ResizeLongestSide -> encoder; caches the embedding."""
         assert image_format in ["RGB", "BGR"], f"image_format must be in ['RGB', 'BGR'], is {image_format}."
         if image_format != self.model.image_format:
             image = image[..., ::-1]
-        resized = self.transform.apply_image(image)
-        # the kernel reads uint8 HWC directly: no permute / float copy on the device
-        t = torch.as_tensor(np.ascontiguousarray(resized), device=self.device)[None]
-        self._encode(t, tuple(image.shape[:2]), tuple(resized.shape[:2]))
+        # H2D of the original pixels, then the resize on the device (bit-exact with the reference's host-side Pillow
+        # resize, oracle/resize_oracle.py); the encoder kernel reads uint8 HWC directly: no permute / float copy
+        src = torch.as_tensor(np.ascontiguousarray(image), device=self.device)
+        resized = self.model.resize_longest_side(src)
+        self._encode(resized[None], tuple(image.shape[:2]), tuple(resized.shape[:2]))
 
     @torch.no_grad()
     def set_torch_image(self, transformed_image: torch.Tensor, original_image_size: Tuple[int, ...]) -> None:

@@ -165,6 +165,36 @@ class Sam:
         return out
 
     @torch.no_grad()
+    def resize_longest_side(self, image: torch.Tensor, out: Optional[torch.Tensor] = None) -> torch.Tensor:
+        """ResizeLongestSide.apply_image on the device (utils/transforms.py:26-31), bit-exact with the Pillow path the
+        reference runs on the host.  image: uint8 [H,W,3] on this device (rows may be strided).  Returns the uint8
+        [h,w,3] image; with `out` (a uint8 [>=h,>=w,3] device container, e.g. one slot of a 1024x1024 batch) the result
+        is written into out[:h,:w] and that view is returned."""
+        from .resize import _scaled_size
+
+        self._require()
+        if image.device != self.device or image.dtype != torch.uint8 or image.dim() != 3 or image.shape[2] != 3:
+            raise RuntimeError(f"resize_longest_side expects uint8 [H,W,3] on {self.device}, got {image.dtype} {tuple(image.shape)}")
+        if image.stride(2) != 1 or image.stride(1) != 3:
+            image = image.contiguous()
+        H, W = int(image.shape[0]), int(image.shape[1])
+        h, w = _scaled_size(H, W, self.cfg.img_size)
+        if out is None and (h, w) == (H, W):
+            return image
+        if out is None:
+            out = torch.empty((h, w, 3), dtype=torch.uint8, device=self.device)
+        elif (out.device != self.device or out.dtype != torch.uint8 or out.dim() != 3 or out.shape[0] < h or out.shape[1] < w
+              or out.shape[2] != 3 or out.stride(2) != 1 or out.stride(1) != 3):
+            raise RuntimeError("resize_longest_side: `out` must be a uint8 [>=h,>=w,3] device tensor with packed pixels")
+        lib = _lib.load()
+        need = int(lib.inksam_resize_workspace_bytes(H, W, h, w))
+        ws = torch.empty(max(need, 1), dtype=torch.uint8, device=self.device)  # stream-ordered: safe to drop after the call
+        with torch.cuda.device(self.device):
+            _lib.check(lib.inksam_resize_u8(_ptr(image), H, W, int(image.stride(0)), _ptr(out), h, w, int(out.stride(0)),
+                                            _ptr(ws), _stream(self.device)))
+        return out[:h, :w]
+
+    @torch.no_grad()
     def decode_boxes(self, embedding: torch.Tensor, boxes: torch.Tensor, input_size: Tuple[int, int],
                      original_size: Tuple[int, int], return_logits: bool = False):
         """prompt encoder + mask decoder + postprocess_masks + threshold for K boxes of one image
@@ -226,6 +256,45 @@ class Sam:
                     h, _ptr(emb), B, _ptr(bx), counts, in_hw, or_hw, _ptr(masks_out), _ptr(iou), _ptr(low), _ptr(None),
                     ctypes.c_float(self.mask_threshold), _stream(dev)))
         return masks_out, iou, low, offsets
+
+    @torch.no_grad()
+    def forward(self, batched_input, multimask_output: bool):
+        """Sam.forward (modeling/sam.py:53-131): the batched entry point.  batched_input: list of dicts with 'image'
+        ([3,h,w], already resized to the model's input frame, values 0..255), 'original_size' (H, W) and 'boxes' ([K,4]
+        xyxy in the input frame).  All images are encoded as one batch and every box of every image is decoded in one
+        pass.  Returns one dict per image: 'masks' bool [K,1,H,W], 'iou_predictions' [K,1], 'low_res_logits'
+        [K,1,256,256].  Box prompts with multimask_output=False only (the surface InkLayer uses)."""
+        if multimask_output:
+            raise NotImplementedError("multimask_output=True is not part of the InkLayer hot path (segmentor/sam.py:35)")
+        S, dev, B = self.cfg.img_size, self.device, len(batched_input)
+        for rec in batched_input:
+            if "point_coords" in rec or "mask_inputs" in rec:
+                raise NotImplementedError("point and mask prompts are not part of the InkLayer hot path (segmentor/sam.py:32-34)")
+            if rec.get("boxes") is None:
+                raise NotImplementedError("Sam.forward needs 'boxes' for every image")
+            im = rec["image"]
+            if im.dim() != 3 or im.shape[0] != 3 or max(im.shape[-2:]) > S:
+                raise RuntimeError(f"'image' must be [3,h,w] with h, w <= {S}, got {tuple(im.shape)}")
+        if B == 0:
+            return []
+        in_sizes = [tuple(int(v) for v in rec["image"].shape[-2:]) for rec in batched_input]
+        sizes = [tuple(int(v) for v in rec["original_size"]) for rec in batched_input]
+        hh, ww = max(s[0] for s in in_sizes), max(s[1] for s in in_sizes)
+        stack = torch.zeros((B, 3, hh, ww), dtype=torch.float32, device=dev)
+        for i, rec in enumerate(batched_input):
+            stack[i, :, :in_sizes[i][0], :in_sizes[i][1]] = rec["image"].to(device=dev, dtype=torch.float32)
+        feats = self.encode(stack, in_sizes)
+        boxes = [rec["boxes"].reshape(-1, 4) for rec in batched_input]
+        masks, iou, low, offs = self.decode_batch(feats, boxes, in_sizes, sizes)
+        out, k0 = [], 0
+        for i in range(B):
+            K, (H, W) = int(boxes[i].shape[0]), sizes[i]
+            m = masks[offs[i]:offs[i] + K * H * W].view(torch.bool).view(K, 1, H, W)
+            out.append({"masks": m, "iou_predictions": iou[k0:k0 + K].view(K, 1), "low_res_logits": low[k0:k0 + K].view(K, 1, 256, 256)})
+            k0 += K
+        return out
+
+    __call__ = forward
 
 
 # ---------------------------------------------------------------------------------------- factories

@@ -191,3 +191,42 @@ def test_vit_l_matches_oracle():
     ious = mask_iou(masks.cpu().numpy(), m_ref.numpy())
     print(f"vit_l: emb rel-RMS {e:.2e}  low-res rel-RMS {lo:.2e}  min IoU {ious.min():.4f}")
     assert e <= 1e-2 and lo <= 1e-2 and ious.min() >= 0.99
+
+
+def test_sam_forward_batched_entry_matches_oracle():
+    """Sam.forward (modeling/sam.py:53-131): list-of-dicts in, list-of-dicts out, images of different input sizes in one
+    batch; checked against the CPU oracle image by image, and the unsupported prompt kinds raise."""
+    from inklayer_b200.resize import ResizeLongestSide
+    from inklayer_b200.synth import synthetic_boxes, synthetic_sketch
+
+    cfg = CONFIGS["vit_tiny"]
+    sd = synthetic_state_dict(cfg, 0)
+    sam = build_sam_from_state_dict(sd, cfg).to("cuda")
+    tr = ResizeLongestSide(1024)
+    shapes = [(600, 750), (1024, 1024), (300, 200)]
+    imgs = [synthetic_sketch(40 + i, *s) for i, s in enumerate(shapes)]
+    boxes = [torch.from_numpy(synthetic_boxes(40 + i, 2 + i, *s)) for i, s in enumerate(shapes)]
+    batch = []
+    for im, bx in zip(imgs, boxes):
+        r = tr.apply_image(im)
+        batch.append({"image": torch.as_tensor(np.ascontiguousarray(r)).permute(2, 0, 1).contiguous().cuda(),
+                      "original_size": im.shape[:2], "boxes": tr.apply_boxes_torch(bx, im.shape[:2]).cuda()})
+    out = sam(batch, multimask_output=False)
+    torch.cuda.synchronize()
+    assert len(out) == len(batch)
+    ora = O.OraclePredictor(O.CONFIGS["vit_tiny"], sd)
+    for i, (im, bx) in enumerate(zip(imgs, boxes)):
+        K, (H, W) = len(bx), shapes[i]
+        o = out[i]
+        assert o["masks"].dtype == torch.bool and tuple(o["masks"].shape) == (K, 1, H, W)
+        assert tuple(o["iou_predictions"].shape) == (K, 1) and tuple(o["low_res_logits"].shape) == (K, 1, 256, 256)
+        ora.set_image(im)
+        m_ref, i_ref, l_ref = ora.predict_torch(O.apply_boxes(bx, im.shape[:2]))
+        assert rel_rms(o["low_res_logits"].cpu(), l_ref) <= 1e-2
+        assert mask_iou(o["masks"][:, 0].cpu().numpy(), m_ref[:, 0].numpy()).min() >= 0.99
+        assert (o["iou_predictions"].cpu() - i_ref).abs().max().item() <= 2e-2
+    with pytest.raises(NotImplementedError):
+        sam(batch, multimask_output=True)
+    with pytest.raises(NotImplementedError):
+        sam([dict(batch[0], point_coords=torch.zeros(1, 1, 2))], multimask_output=False)
+    assert sam([], multimask_output=False) == []

@@ -117,3 +117,42 @@ def test_postprocess_matches_interpolate(inp, orig):
                                              ctypes.c_float(0.0), stream()))
         assert torch.equal(buf[shift:shift + K * H * W].view(K, 1, H, W), masks)
         assert (buf[:shift] == 7).all() and (buf[shift + K * H * W:] == 7).all()  # nothing written outside
+
+
+@pytest.mark.parametrize("hw", [(750, 750), (600, 750), (300, 200), (1333, 751), (2000, 1500), (64, 1000), (37, 53), (1025, 1024),
+                                (1, 7), (777, 3001), (1024, 512)])
+def test_resize_u8_bit_exact_with_pillow_oracle(hw):
+    """inksam_resize_u8 (ResizeLongestSide.apply_image on the device) into a 1024x1024x3 container vs the Pillow
+    restatement (oracle/resize_oracle.py): identical bytes, nothing written outside the [h, w] window."""
+    from oracle import resize_oracle as R
+
+    lib = _lib.load()
+    img = np.random.default_rng(hw[0] * 7 + hw[1]).integers(0, 256, hw + (3,), dtype=np.uint8)
+    ref = R.apply_image(img)
+    h, w = ref.shape[:2]
+    src = torch.from_numpy(img).cuda()
+    dst = torch.full((1024, 1024, 3), 9, dtype=torch.uint8, device="cuda")
+    need = lib.inksam_resize_workspace_bytes(hw[0], hw[1], h, w)
+    ws = torch.empty(max(int(need), 1), dtype=torch.uint8, device="cuda")
+    _lib.check(lib.inksam_resize_u8(ptr(src), hw[0], hw[1], hw[1] * 3, ptr(dst), h, w, 1024 * 3, ptr(ws), stream()))
+    got = dst.cpu().numpy()
+    assert np.array_equal(got[:h, :w], ref)
+    assert (got[h:] == 9).all() and (got[:, w:] == 9).all()
+
+
+def test_sam_resize_longest_side_and_errors():
+    from inklayer_b200 import CONFIGS, build_sam_from_state_dict
+    from inklayer_b200.weights import synthetic_state_dict
+    from oracle import resize_oracle as R
+
+    cfg = CONFIGS["vit_tiny"]
+    sam = build_sam_from_state_dict(synthetic_state_dict(cfg, 0), cfg).to("cuda")
+    img = np.random.default_rng(11).integers(0, 256, (500, 380, 3), dtype=np.uint8)
+    got = sam.resize_longest_side(torch.from_numpy(img).cuda())
+    assert np.array_equal(got.cpu().numpy(), R.apply_image(img))
+    same = torch.from_numpy(np.zeros((1024, 700, 3), np.uint8)).cuda()
+    assert sam.resize_longest_side(same) is same  # already in the input frame
+    with pytest.raises(RuntimeError):
+        sam.resize_longest_side(torch.zeros(3, 10, 10, dtype=torch.uint8, device="cuda"))
+    lib = _lib.load()
+    assert lib.inksam_resize_u8(None, 10, 10, 30, None, 5, 5, 15, None, stream()) != 0
