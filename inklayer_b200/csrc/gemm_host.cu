@@ -39,6 +39,21 @@ int make_tmap_2d(CUtensorMap* out, const void* base, int elem_bytes, uint64_t ro
   return 0;
 }
 
+// fp32 row-major [rows][cols] output matrix for the staged epilogue: box = 16 columns (64 bytes) x 32 rows, 64B swizzle.
+int make_tmap_f32_out(CUtensorMap* out, const void* base, uint64_t rows, uint64_t cols, uint64_t ld_elems) {
+  if (fetch_encode()) return set_error("cuTensorMapEncodeTiled entry point not available");
+  cuuint64_t dims[2] = {cols, rows};
+  cuuint64_t strides[1] = {ld_elems * 4};
+  cuuint32_t box[2] = {16, 32};
+  cuuint32_t estr[2] = {1, 1};
+  CUresult r = g_encode(out, CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 2, const_cast<void*>(base), dims, strides, box, estr,
+                        CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_64B, CU_TENSOR_MAP_L2_PROMOTION_NONE,
+                        CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+  if (r != CUDA_SUCCESS) return set_error("cuTensorMapEncodeTiled(f32 out) failed: %d (rows=%llu cols=%llu ld=%llu)", (int)r,
+                                          (unsigned long long)rows, (unsigned long long)cols, (unsigned long long)ld_elems);
+  return 0;
+}
+
 // bf16 row-major [rows][cols] matrix, arbitrary box; swizzle 128B (box_cols == 64) or 32B (box_cols == 16).
 int make_tmap_bf16_box(CUtensorMap* out, const void* base, uint64_t rows, uint64_t cols, uint64_t ld_elems,
                        uint32_t box_cols, uint32_t box_rows) {
@@ -72,8 +87,9 @@ int make_tmap_conv3(CUtensorMap* out, const void* base, int nb, int C) {
 }
 
 template <int CG, int TF32, int BN, int EPI>
-static int launch_one(const CUtensorMap& tA, const CUtensorMap& tB, const GemmArgs& g, int num_sms, cudaStream_t st) {
-  using C = GemmCfg<CG, TF32, BN>;
+static int launch_one(const CUtensorMap& tA, const CUtensorMap& tB, const CUtensorMap& tO, const GemmArgs& g, int num_sms,
+                      cudaStream_t st) {
+  using C = GemmCfg<CG, TF32, BN, gemm_staged(EPI)>;
   auto kern = gemm_tc_kernel<CG, TF32, BN, EPI>;
   static bool attr_done = false;
   if (!attr_done) {
@@ -106,13 +122,13 @@ static int launch_one(const CUtensorMap& tA, const CUtensorMap& tB, const GemmAr
   int clusters = max_clusters;
   if (tiles < clusters) clusters = tiles;
   cfg.gridDim = dim3(clusters * CG);
-  CUDA_TRY(cudaLaunchKernelEx(&cfg, kern, tA, tB, g));
+  CUDA_TRY(cudaLaunchKernelEx(&cfg, kern, tA, tB, tO, g));
   return 0;
 }
 
 #define GEMM_CASE(CG_, TF_, BN_, EPI_)                                             \
   if (cg == CG_ && tf32 == TF_ && bn == BN_ && epi == EPI_)                        \
-    return launch_one<CG_, TF_, BN_, EPI_>(tA, tB, g, num_sms, st);
+    return launch_one<CG_, TF_, BN_, EPI_>(tA, tB, tO, g, num_sms, st);
 
 // A: [M][K] (ld = lda elements) or the padded conv map when g.a_conv3x3; W: [N][K] row-major.
 int launch_gemm(int cg, int tf32, int bn, int epi, const void* A, int lda, const void* W, int ldw, GemmArgs g,
@@ -127,6 +143,12 @@ int launch_gemm(int cg, int tf32, int bn, int epi, const void* A, int lda, const
     if (make_tmap_2d(&tA, A, esz, g.M, g.K, lda, 128)) return -1;
   }
   if (make_tmap_2d(&tB, W, esz, g.N, g.K, ldw, bn / cg)) return -1;
+  CUtensorMap tO = tA;  // only the staged fp32 residual epilogue stores through a tensor map
+  if (gemm_staged(epi)) {
+    if ((reinterpret_cast<uintptr_t>(g.out) & 15) != 0 || (g.ldo * 4) % 16 != 0)
+      return set_error("gemm: the residual epilogue needs a 16-byte aligned output (ldo=%d)", g.ldo);
+    if (make_tmap_f32_out(&tO, g.out, g.M, g.N, g.ldo)) return -1;
+  }
 
   GEMM_CASE(1, 0, 256, EPI_BIAS_BF16)
   GEMM_CASE(2, 0, 256, EPI_BIAS_BF16)

@@ -47,27 +47,36 @@ __host__ __device__ constexpr int gemm_epi_warps(int epi) {
   return (epi == EPI_LN_BF16_PAD || epi == EPI_LN_F32_NCHW) ? 4 : 8;
 }
 
-template <int CG, int TF32, int BN>
+// ST != 0 (the fp32 residual epilogue): every epilogue warp owns two 2 KB staging buffers from which its 32-row x
+// 16-column fp32 sub-tiles leave by TMA store (32 KB in all; the CTA-pair ring keeps its 6 stages of 32 KB).
+template <int CG, int TF32, int BN, int ST = 0>
 struct GemmCfg {
   static constexpr int BM = 128;                 // rows per CTA (UMMA M = BM * CG)
   static constexpr int BNL = BN / CG;            // W rows loaded by each CTA
   static constexpr int A_BYTES = BM * 128;       // one stage of A: 128 rows x 128 bytes
   static constexpr int B_BYTES = BNL * 128;
   static constexpr int STAGE_BYTES = A_BYTES + B_BYTES;
-  static constexpr int STAGES = (192 * 1024) / STAGE_BYTES > 8 ? 8 : (192 * 1024) / STAGE_BYTES;
+  static constexpr int STAGING_BYTES = ST ? 8 * 2 * 2048 : 0;
+  static constexpr int AUX_BYTES = ST ? 256 /*barriers*/ : 256 /*barriers*/ + 4096 /*LN partials*/ + 1024 /*epilogue constants*/;
+  static constexpr int RING_BUDGET = ST ? (227 * 1024 - 1024 - AUX_BYTES - STAGING_BYTES) : 192 * 1024;
+  static constexpr int STAGES = RING_BUDGET / STAGE_BYTES > 8 ? 8 : RING_BUDGET / STAGE_BYTES;
   static constexpr int KELEMS = TF32 ? 32 : 64;  // elements per 128-byte smem row
-  static constexpr int SMEM_BYTES = STAGES * STAGE_BYTES + 1024 /*align slack*/ + 256 /*barriers*/ + 4096 /*LN partials*/ + 1024 /*epilogue constants*/;
+  static constexpr int SMEM_BYTES = STAGES * STAGE_BYTES + STAGING_BYTES + 1024 /*align slack*/ + AUX_BYTES;
   static constexpr uint32_t IDESC = make_idesc(TF32 ? 2u : 1u, BM * CG, BN);
   static constexpr int TMEM_COLS = 2 * BN;       // double-buffered accumulators (power of two: 256 or 512)
 };
 
+__host__ __device__ constexpr int gemm_staged(int epi) { return epi == EPI_BIAS_RESID_F32 ? 1 : 0; }
+
 template <int CG, int TF32, int BN, int EPI>
 __global__ void __launch_bounds__(384, 1)
-gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB, const GemmArgs g) {
-  using C = GemmCfg<CG, TF32, BN>;
+gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB,
+               const __grid_constant__ CUtensorMap tmO, const GemmArgs g) {
+  using C = GemmCfg<CG, TF32, BN, gemm_staged(EPI)>;
   extern __shared__ uint8_t smem_raw[];
   const uint32_t smem_base = (smem_u32(smem_raw) + 1023u) & ~1023u;
-  const uint32_t bar_base = smem_base + C::STAGES * C::STAGE_BYTES;
+  const uint32_t staging_base = smem_base + C::STAGES * C::STAGE_BYTES;  // 1024-byte aligned (stages are 16 KB multiples)
+  const uint32_t bar_base = staging_base + C::STAGING_BYTES;
   auto full_bar = [&](int s) { return bar_base + 8u * s; };
   auto empty_bar = [&](int s) { return bar_base + 8u * (C::STAGES + s); };
   auto tfull_bar = [&](int s) { return bar_base + 8u * (2 * C::STAGES + s); };
@@ -109,7 +118,7 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
   }
   // per-channel constants of the conv-transpose epilogue, read back with volatile broadcast LDS.128 so that the
   // compiler does not hoist 192 loop-invariant values into registers
-  const uint32_t econst = bar_base + 256 + 4096;
+  const uint32_t econst = bar_base + 256 + 4096;  // (not present in the staged layout, which has no such epilogue)
   if constexpr (EPI == EPI_UPSCALE1) {
     float* ec = reinterpret_cast<float*>(smem_raw + (econst - smem_u32(smem_raw)));
     if (threadIdx.x >= 128 && threadIdx.x < 192) {
@@ -235,10 +244,79 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
           for (int h = 0; h < 4; ++h) ld_global_v8(add_row + c_first * 32 + h * 8, *reinterpret_cast<uint32_t(*)[8]>(&radd[0][h * 8]));
         }
       }
+      if constexpr (EPI == EPI_BIAS_RESID_F32) {
+        // The fp32 residual is the dominant HBM stream of the short-K GEMMs (attn.proj: K = 1280) and register
+        // prefetch keeps only one 128-byte line per thread in flight.  Pull the NEXT tile's share of this thread's row
+        // (NCW lines) into L2 now, a whole tile ahead of its use: the later loads find it on chip.
+        const int nt = tile + num_clusters;
+        if (nt < num_tiles) {
+          const int nm = (nt / tiles_n) * C::BM * CG + (int)rank * C::BM + q * 32 + lane;
+          const int nn0 = (nt % tiles_n) * BN;
+          if (nm < g.M) {
+            const float* nrow = g.resid + (size_t)nm * g.ldo + nn0 + c_first * 32;
+#pragma unroll
+            for (int ci = 0; ci < NCW; ++ci)
+              if (nn0 + (c_first + ci) * 32 < g.N) prefetch_l2(nrow + ci * 32);
+          }
+        }
+      }
+      [[maybe_unused]] float4 bq = make_float4(0.f, 0.f, 0.f, 0.f);
+      if constexpr (EPI == EPI_BIAS_RESID_F32) {
+        if (g.bias != nullptr && n0 + c_first * 32 + lane * 4 < g.N)
+          bq = __ldg(reinterpret_cast<const float4*>(g.bias + n0 + c_first * 32 + lane * 4));
+      }
       mbar_wait(tfull_bar(as), aphase);
       tc_fence_after();
 
-      if constexpr (kSimple) {
+      if constexpr (EPI == EPI_BIAS_RESID_F32) {
+        // out = resid + acc + bias, fp32.  Thread-per-row global stores of a 32 x 32 fp32 sub-tile touch 32 lines per
+        // instruction; instead each warp writes 32 x 16 halves into 64B-swizzled staging buffers (conflict-free 16-byte
+        // stores) and one lane sends them out with TMA stores.  Two buffers per warp: a buffer is rewritten once the
+        // store issued from it two halves earlier has read it (bulk async-group wait).
+        // The warp's 128 bias values live 4 per lane and are broadcast by shuffles: with the L1 reduced to ~28 KB by
+        // the smem ring and streamed through by the residual, per-chunk bias loads miss to L2 on the critical path.
+        uint32_t v[32];
+        float* f = reinterpret_cast<float*>(v);
+        const uint32_t sbuf = staging_base + (uint32_t)(warp - 4) * 4096u;
+        const int row0 = m - lane;
+        const uint32_t srow = (uint32_t)lane * 64u, sx = (uint32_t)((lane >> 1) & 3);
+#pragma unroll
+        for (int ci = 0; ci < NCW; ++ci) {
+          const int c = c_first + ci;
+          const int col = n0 + c * 32;
+          if (col < g.N) {  // warp-uniform
+            tmem_ld_32x32(taddr + c * 32, v);
+            if (ci + 1 < NCW && col + 32 < g.N) {
+#pragma unroll
+              for (int h = 0; h < 4; ++h)
+                ld_global_v8(add_row + (c + 1) * 32 + h * 8, *reinterpret_cast<uint32_t(*)[8]>(&radd[(ci + 1) & 1][h * 8]));
+            }
+            tmem_ld_wait();
+#pragma unroll
+            for (int hf = 0; hf < 2; ++hf) {
+              if (lane == 0) bulk_wait_group_read<1>();
+              __syncwarp();
+              const uint32_t sb = sbuf + (uint32_t)hf * 2048u;
+#pragma unroll
+              for (int j = 0; j < 4; ++j) {
+                const int e = hf * 16 + 4 * j;          // column of the chunk
+                const int src = ci * 8 + hf * 4 + j;    // lane holding bias[e .. e+3] of this warp's columns
+                const float x0 = f[e] + __shfl_sync(0xffffffffu, bq.x, src) + __uint_as_float(radd[ci & 1][e]);
+                const float x1 = f[e + 1] + __shfl_sync(0xffffffffu, bq.y, src) + __uint_as_float(radd[ci & 1][e + 1]);
+                const float x2 = f[e + 2] + __shfl_sync(0xffffffffu, bq.z, src) + __uint_as_float(radd[ci & 1][e + 2]);
+                const float x3 = f[e + 3] + __shfl_sync(0xffffffffu, bq.w, src) + __uint_as_float(radd[ci & 1][e + 3]);
+                st_shared_v4(sb + srow + (((uint32_t)j ^ sx) << 4), x0, x1, x2, x3);
+              }
+              fence_proxy_async_smem();
+              __syncwarp();
+              if (lane == 0) {
+                tma_store_2d(&tmO, sb, col + hf * 16, row0);
+                bulk_commit_group();
+              }
+            }
+          }
+        }
+      } else if constexpr (kSimple) {
         uint32_t v[32];
         float* f = reinterpret_cast<float*>(v);
 #pragma unroll
@@ -535,6 +613,9 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
   }
 
   // ---------------------------------------------------------------- teardown
+  if constexpr (EPI == EPI_BIAS_RESID_F32) {
+    if (warp >= 4 && lane == 0) bulk_wait_group_all();  // this warp's TMA stores have left shared memory and are complete
+  }
   tc_fence_before();
   if constexpr (CG == 2) cluster_sync_all(); else __syncthreads();
   tc_fence_after();

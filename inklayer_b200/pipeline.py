@@ -61,7 +61,8 @@ class SketchSegmenter:
         self._slots = [_Slot(sam, max_batch) for _ in range(self.depth + 1)]
         with torch.cuda.device(sam.device):
             self._s_in, self._s_run, self._s_out = torch.cuda.Stream(), torch.cuda.Stream(), torch.cuda.Stream()
-        self._pool = ThreadPoolExecutor(max_workers=1)
+        self._pool = ThreadPoolExecutor(max_workers=1)        # one hand-off per batch, in order
+        self._copy_pool = ThreadPoolExecutor(max_workers=4)   # per-image copies out of pinned memory (numpy drops the GIL)
         self._next = 0
         self.h2d_bytes = 0
         self.d2h_bytes = 0
@@ -130,15 +131,16 @@ class SketchSegmenter:
         slot.views = [(offs[i], counts[i], sizes[i]) for i in range(B)]
         return slot
 
-    @staticmethod
-    def _collect(slot: _Slot) -> List[np.ndarray]:
+    def _collect(self, slot: _Slot) -> List[np.ndarray]:
         """Waits for the batch's D2H copy and hands every image's masks to the caller as its own bool array."""
         slot.ev_out.synchronize()
         host = slot.host_masks.numpy()
-        out = []
-        for off, k, (H, W) in slot.views:
-            out.append(host[off:off + k * H * W].view(np.bool_).reshape(k, H, W).copy())
-        return out
+
+        def own(view) -> np.ndarray:
+            off, k, (H, W) = view
+            return host[off:off + k * H * W].view(np.bool_).reshape(k, H, W).copy()
+
+        return list(self._copy_pool.map(own, slot.views))
 
     # ------------------------------------------------------------------ public API
     @torch.no_grad()

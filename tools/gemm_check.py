@@ -51,10 +51,13 @@ def run_group(group):
 
     ok = True
     if "perf" in group:
-        for (M, N, K, epi) in [(32768, 3840, 1280, 0), (32768, 1280, 1280, 2), (32768, 5120, 1280, 1),
-                               (32768, 1280, 5120, 2), (4096, 5120, 1280, 1)]:
+        shapes = [(32768, 3840, 1280, 0), (32768, 1280, 1280, 2), (32768, 5120, 1280, 1), (32768, 1280, 5120, 2),
+                  (4096, 5120, 1280, 1)]
+        if "proj" in group:  # which part of the attn.proj epilogue costs: bf16 store / fp32 store / fp32 store + residual
+            shapes = [(32768, 1280, 1280, 0), (32768, 1280, 1280, 7), (32768, 1280, 1280, 2)]
+        for (M, N, K, epi) in shapes:
             A = rnd(M, K).to(dt); W = rnd(N, K, scale=0.03).to(dt); bias = rnd(N)
-            out = torch.empty(M, N, device=dev, dtype=torch.float32 if epi == 2 else torch.bfloat16)
+            out = torch.empty(M, N, device=dev, dtype=torch.float32 if epi in (2, 7) else torch.bfloat16)
             resid = torch.zeros(M, N, device=dev) if epi == 2 else None
             for _ in range(3):
                 gemm(lib, cg, tf32, 256, epi, A, W, out, bias=bias, resid=resid)
