@@ -41,6 +41,15 @@ def measured_peaks():
     return 1400.0, 6650.0, "fallback"
 
 
+def gemm_traffic():
+    """DRAM bytes per encoder-GEMM launch from the committed `ncu --set full` capture (tools/ncu_summary.py traffic);
+    None if no capture has been summarised."""
+    p = os.path.join(ROOT, "profiles", "gemm_traffic.json")
+    if not os.path.exists(p):
+        return None
+    return json.load(open(p)).get("dram_bytes_per_launch")
+
+
 class ClockSampler:
     """nvidia-smi clocks / throttle reasons sampled every 200 ms while the timed region runs."""
 
@@ -231,6 +240,11 @@ def run_b200(args):
         peak_tf, peak_gbs, peak_src = measured_peaks()
         n_sk = BATCH * world * args.steps
         g_ms, g_flop, g_n = prof["encoder_gemm"]
+        # algorithmic HBM bytes of the 4 GEMMs of a ViT block at this batch (A + W + output, + fp32 residual for proj / lin2)
+        M, D = BATCH * 4096, cfg.embed_dim
+        blk = ((M * D * 2 + 3 * D * D * 2 + M * 3 * D * 2) + (M * D * 2 + D * D * 2 + 2 * M * D * 4) +
+               (M * D * 2 + 4 * D * D * 2 + M * 4 * D * 2) + (M * 4 * D * 2 + 4 * D * D * 2 + 2 * M * D * 4))
+        g_bytes = blk * cfg.depth * args.steps
         a_ms, a_flop, a_n = prof["encoder_attention"]
         d_ms, d_flop, d_n = prof["decoder_gemm"]
         p_ms, p_bytes, p_n = prof["postprocess"]
@@ -249,7 +263,9 @@ def run_b200(args):
                     "d2h_bytes_per_step": seg.d2h_bytes // args.steps},
             "gpu_launches": launches,
             "roofline": {"bound": "tensor", "kernel": "gemm_tc_kernel (encoder instantiations)", "achieved": achieved, "peak": peak_tf,
-                         "unit": "TFLOP/s", "frac": achieved / peak_tf, "traffic": None, "peak_source": peak_src + " sustained bf16",
+                         "unit": "TFLOP/s", "frac": achieved / peak_tf, "traffic": gemm_traffic(),
+                         "traffic_unit": "DRAM bytes per launch (ncu dram__bytes_read.sum + dram__bytes_write.sum, profiles/gemm_traffic.json)",
+                         "algorithmic_bytes_per_launch": g_bytes / max(g_n, 1), "peak_source": peak_src + " sustained bf16",
                          "launches": g_n, "avg_launch_ms": g_ms / max(g_n, 1), "share_of_step": g_ms / ms},
             "encoder": {"ms_per_batch": ms_enc / args.steps, "images_per_s": BATCH * args.steps / (ms_enc * 1e-3),
                         "tflops": enc_tf, "frac_of_peak": enc_tf / peak_tf,

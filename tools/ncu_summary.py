@@ -3,6 +3,7 @@
 
     tools/ncu_summary.py launches gpurun_out/launches.csv            # per-kernel totals of a launch list
     tools/ncu_summary.py full gpurun_out/prof_gemm.ncu-rep [...]     # key metrics of every launch in --set full reports
+    tools/ncu_summary.py traffic gpurun_out/prof_gemm.ncu-rep out.json  # mean DRAM bytes per launch (bench.py roofline.traffic)
 """
 import collections
 import csv
@@ -66,8 +67,31 @@ def full(paths) -> None:
         print()
 
 
+def traffic(path: str, out_json: str) -> None:
+    """Mean of dram__bytes_read.sum + dram__bytes_write.sum over the bf16 encoder GEMM launches of a --set full capture
+    (a whole number of layers: qkv, proj, lin1, lin2 repeating)."""
+    import json
+
+    out = subprocess.run(["ncu", "-i", path, "--page", "raw", "--csv"], capture_output=True, text=True).stdout
+    rows = list(csv.reader(io.StringIO(out)))
+    hdr, units = rows[0], rows[1]
+    ir, iw, ik = hdr.index("dram__bytes_read.sum"), hdr.index("dram__bytes_write.sum"), hdr.index("Kernel Name")
+    scale = {"byte": 1.0, "Kbyte": 1e3, "Mbyte": 1e6, "Gbyte": 1e9}
+    per = []
+    for row in rows[2:]:
+        name = short(row[ik])
+        if not re.match(r"gemm_tc_kernel<\d, 0,", name):   # bf16 instantiations = the encoder
+            continue
+        per.append({"kernel": name, "bytes": float(row[ir]) * scale[units[ir]] + float(row[iw]) * scale[units[iw]]})
+    mean = sum(p["bytes"] for p in per) / max(len(per), 1)
+    json.dump({"source": path, "launches": len(per), "dram_bytes_per_launch": mean, "per_launch": per}, open(out_json, "w"), indent=1)
+    print(f"{len(per)} launches, mean DRAM traffic {mean / 1e6:.1f} MB per launch -> {out_json}")
+
+
 if __name__ == "__main__":
     if sys.argv[1] == "launches":
         launches(sys.argv[2])
+    elif sys.argv[1] == "traffic":
+        traffic(sys.argv[2], sys.argv[3])
     else:
         full(sys.argv[2:])
