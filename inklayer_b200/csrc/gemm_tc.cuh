@@ -244,22 +244,6 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
           for (int h = 0; h < 4; ++h) ld_global_v8(add_row + c_first * 32 + h * 8, *reinterpret_cast<uint32_t(*)[8]>(&radd[0][h * 8]));
         }
       }
-      if constexpr (EPI == EPI_BIAS_RESID_F32) {
-        // The fp32 residual is the dominant HBM stream of the short-K GEMMs (attn.proj: K = 1280) and register
-        // prefetch keeps only one 128-byte line per thread in flight.  Pull the NEXT tile's share of this thread's row
-        // (NCW lines) into L2 now, a whole tile ahead of its use: the later loads find it on chip.
-        const int nt = tile + num_clusters;
-        if (nt < num_tiles) {
-          const int nm = (nt / tiles_n) * C::BM * CG + (int)rank * C::BM + q * 32 + lane;
-          const int nn0 = (nt % tiles_n) * BN;
-          if (nm < g.M) {
-            const float* nrow = g.resid + (size_t)nm * g.ldo + nn0 + c_first * 32;
-#pragma unroll
-            for (int ci = 0; ci < NCW; ++ci)
-              if (nn0 + (c_first + ci) * 32 < g.N) prefetch_l2(nrow + ci * 32);
-          }
-        }
-      }
       [[maybe_unused]] float4 bq = make_float4(0.f, 0.f, 0.f, 0.f);
       if constexpr (EPI == EPI_BIAS_RESID_F32) {
         if (g.bias != nullptr && n0 + c_first * 32 + lane * 4 < g.N)

@@ -7,7 +7,7 @@ EPI = dict(BIAS_BF16=0, GELU=1, RESID=2, ROWADD=3, LN_PAD=4, LN_NCHW=5, RESID_LN
 
 
 def load():
-    lib = ctypes.CDLL(os.path.join(ROOT, "inklayer_b200", "libinksam.so"))
+    lib = ctypes.CDLL(os.environ.get("INKSAM_LIB", os.path.join(ROOT, "inklayer_b200", "libinksam.so")))
     lib.inksam_last_error.restype = ctypes.c_char_p
     return lib
 
