@@ -256,18 +256,33 @@ int launch_decoder_tokens(const DecWeights& w, const DecState& s, int boxes, int
 // 7 queries x 4096 keys per (box, head), internal dim 128 = 8 heads x 16 (downsample_rate 2, transformer.py:204-206).
 // kv rows: [4096][ld] fp32 with k at column 0 and v at column 128 (+ head*16); box_stride 0 when all boxes share keys.
 // box_img != null: the keys of box b are those of image box_img[b] (kv + box_img[b] * box_stride), shared by its boxes.
+//
+// HBM-bound (the per-box keys are read once: 4 MB per box and launch).  A CTA takes 512 consecutive keys of one box for
+// ALL heads: thread = (key row of a 32-row pass, head), so the 8 threads of a key read its 512 contiguous bytes of k
+// and of v and the CTA streams one contiguous 512-row range (a CTA per (box, head) read 64-byte slices at a 1-1.5 KB
+// stride and sat at a third of the HBM peak on DRAM page misses).  The 8 key ranges of a box are merged by the last
+// CTA to finish (ticket counter), in fixed order, so the result does not depend on scheduling.
+constexpr int T2I_SPLITS = 8;                       // key ranges per box
+constexpr int T2I_PART = 8 * NT * 18;               // floats of one partial: [head][token][16 acc, l, m]
+constexpr int T2I_QP = 20;                          // padded head row of q in shared memory (conflict-free LDS.128)
+
 __global__ void __launch_bounds__(256) decoder_t2i_kernel(const float* __restrict__ q, const float* __restrict__ kv,
                                                           long long box_stride, int ld, const int* __restrict__ box_img,
-                                                          float* __restrict__ out) {
-  const int box = blockIdx.x >> 3, h = blockIdx.x & 7, tid = threadIdx.x;
-  __shared__ __align__(16) float qs[NT][16];
-  __shared__ float red_m[8][NT];
-  __shared__ float red[8][NT * 17];
-  if (tid < NT * 16)  // 1/sqrt(16) and log2(e) folded into q
-    qs[tid / 16][tid % 16] = q[(size_t)box * NT * 128 + (tid / 16) * 128 + h * 16 + tid % 16] * (0.25f * 1.4426950408889634f);
+                                                          float* __restrict__ out, float* __restrict__ partial,
+                                                          int* __restrict__ ticket) {
+  const int box = blockIdx.y, split = blockIdx.x, tid = threadIdx.x;
+  const int h = tid & 7, kr = tid >> 3, warp = tid >> 5, lane = tid & 31;
+  __shared__ __align__(16) float qs[NT * 8 * T2I_QP];
+  __shared__ float red_m[8][8 * NT];
+  __shared__ float red[8][8 * NT * 17];
+  __shared__ int last;
+  for (int i = tid; i < NT * 128; i += 256) {  // 1/sqrt(16) and log2(e) folded into q
+    const int t = i >> 7, c = i & 127;
+    qs[(t * 8 + (c >> 4)) * T2I_QP + (c & 15)] = q[(size_t)box * NT * 128 + i] * (0.25f * 1.4426950408889634f);
+  }
   __syncthreads();
-  const float* base = kv + (size_t)(box_img ? box_img[box] : box) * box_stride + h * 16;
-  const uint32_t qs_addr = (uint32_t)__cvta_generic_to_shared(&qs[0][0]);
+  const float* base = kv + (size_t)(box_img ? box_img[box] : box) * box_stride + (size_t)split * 512 * ld + h * 16;
+  const uint32_t qs_addr = (uint32_t)__cvta_generic_to_shared(&qs[0]) + (uint32_t)(h * T2I_QP * 4);
   float m[NT], l[NT], acc[NT][16];
 #pragma unroll
   for (int t = 0; t < NT; ++t) {
@@ -275,39 +290,39 @@ __global__ void __launch_bounds__(256) decoder_t2i_kernel(const float* __restric
 #pragma unroll
     for (int d = 0; d < 16; ++d) acc[t][d] = 0.f;
   }
-  // Each thread walks 16 keys (stride 256) with the next key's k / v rows already in flight.  The softmax shift of a
-  // token is lazy: it is set by the first key and moves (with an exact rescale of l and acc) only when a later score
-  // exceeds it by more than 2^24, so the common path is one exp2 and 17 FMAs per (token, key).
+  // 16 passes of 32 keys with the next pass already in flight.  The softmax shift of a token is lazy: it is set by the
+  // first key and moves (with an exact rescale of l and acc) only when a later score exceeds it by more than 2^24, so
+  // the common path is one exp2 and 17 FMAs per (token, key).
   float4 nk[4], nv[4];
   {
-    const float4* kr = reinterpret_cast<const float4*>(base + (size_t)tid * ld);
+    const float4* r = reinterpret_cast<const float4*>(base + (size_t)kr * ld);
 #pragma unroll
-    for (int i = 0; i < 4; ++i) { nk[i] = kr[i]; nv[i] = kr[32 + i]; }
+    for (int i = 0; i < 4; ++i) { nk[i] = r[i]; nv[i] = r[32 + i]; }
   }
 #pragma unroll 1
-  for (int j = tid; j < 4096; j += 256) {
+  for (int j = kr; j < 512; j += 32) {
     float kk[16], vv[16];
 #pragma unroll
     for (int i = 0; i < 4; ++i) {
       kk[4 * i] = nk[i].x; kk[4 * i + 1] = nk[i].y; kk[4 * i + 2] = nk[i].z; kk[4 * i + 3] = nk[i].w;
       vv[4 * i] = nv[i].x; vv[4 * i + 1] = nv[i].y; vv[4 * i + 2] = nv[i].z; vv[4 * i + 3] = nv[i].w;
     }
-    if (j + 256 < 4096) {
-      const float4* kr = reinterpret_cast<const float4*>(base + (size_t)(j + 256) * ld);
+    if (j + 32 < 512) {
+      const float4* r = reinterpret_cast<const float4*>(base + (size_t)(j + 32) * ld);
 #pragma unroll
-      for (int i = 0; i < 4; ++i) { nk[i] = kr[i]; nv[i] = kr[32 + i]; }
+      for (int i = 0; i < 4; ++i) { nk[i] = r[i]; nv[i] = r[32 + i]; }
     }
 #pragma unroll
     for (int t = 0; t < NT; ++t) {
       float sc = 0.f;
 #pragma unroll
       for (int i = 0; i < 4; ++i) {
-        // q stays in shared memory (broadcast LDS.128, re-read per key): hoisted into registers it would be 112
-        // more live values on top of the 112 accumulators
+        // q stays in shared memory (LDS.128, re-read per key): in registers it would be 112 more live values on top
+        // of the 112 accumulators
         float4 q4;
         asm volatile("ld.shared.v4.f32 {%0, %1, %2, %3}, [%4];"
                      : "=f"(q4.x), "=f"(q4.y), "=f"(q4.z), "=f"(q4.w)
-                     : "r"(qs_addr + (uint32_t)((t * 16 + 4 * i) * 4)));
+                     : "r"(qs_addr + (uint32_t)((t * 8 * T2I_QP + 4 * i) * 4)));
         sc += q4.x * kk[4 * i] + q4.y * kk[4 * i + 1] + q4.z * kk[4 * i + 2] + q4.w * kk[4 * i + 3];
       }
       if (sc > m[t] + 24.f) {  // first key (m = -inf) or a much larger score: move the shift
@@ -323,55 +338,92 @@ __global__ void __launch_bounds__(256) decoder_t2i_kernel(const float* __restric
       for (int d = 0; d < 16; ++d) acc[t][d] += p * vv[d];
     }
   }
-  // merge the 256 partial softmaxes: block max, rescale, block sum
-  const int warp = tid >> 5, lane = tid & 31;
+  // merge the 32 partial softmaxes of every head: the lanes of a warp with equal (lane & 7) share a head
   float gm[NT];
 #pragma unroll
   for (int t = 0; t < NT; ++t) {
     float v = m[t];
-#pragma unroll
-    for (int o = 16; o > 0; o >>= 1) v = fmaxf(v, __shfl_xor_sync(0xffffffffu, v, o));
-    if (lane == 0) red_m[warp][t] = v;
+    v = fmaxf(v, __shfl_xor_sync(0xffffffffu, v, 8));
+    v = fmaxf(v, __shfl_xor_sync(0xffffffffu, v, 16));
+    if (lane < 8) red_m[warp][h * NT + t] = v;
   }
   __syncthreads();
 #pragma unroll
   for (int t = 0; t < NT; ++t) {
-    float v = red_m[0][t];
+    float v = red_m[0][h * NT + t];
 #pragma unroll
-    for (int w2 = 1; w2 < 8; ++w2) v = fmaxf(v, red_m[w2][t]);
+    for (int w2 = 1; w2 < 8; ++w2) v = fmaxf(v, red_m[w2][h * NT + t]);
     gm[t] = v;
   }
 #pragma unroll
   for (int t = 0; t < NT; ++t) {
     const float sc = exp2f(m[t] - gm[t]);
     float v = l[t] * sc;
-#pragma unroll
-    for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
-    if (lane == 0) red[warp][t * 17 + 16] = v;
+    v += __shfl_xor_sync(0xffffffffu, v, 8);
+    v += __shfl_xor_sync(0xffffffffu, v, 16);
+    if (lane < 8) red[warp][(h * NT + t) * 17 + 16] = v;
 #pragma unroll
     for (int d = 0; d < 16; ++d) {
       float a = acc[t][d] * sc;
-#pragma unroll
-      for (int o = 16; o > 0; o >>= 1) a += __shfl_xor_sync(0xffffffffu, a, o);
-      if (lane == 0) red[warp][t * 17 + d] = a;
+      a += __shfl_xor_sync(0xffffffffu, a, 8);
+      a += __shfl_xor_sync(0xffffffffu, a, 16);
+      if (lane < 8) red[warp][(h * NT + t) * 17 + d] = a;
     }
   }
   __syncthreads();
-  if (tid < NT * 16) {
-    const int t = tid / 16, d = tid % 16;
+  // this key range's partial: [head][token][16 acc, l, m]
+  float* part = partial + ((size_t)box * T2I_SPLITS + split) * T2I_PART;
+  for (int i = tid; i < 8 * NT * 17; i += 256) {
+    float a = 0.f;
+#pragma unroll
+    for (int w2 = 0; w2 < 8; ++w2) a += red[w2][i];
+    part[(i / 17) * 18 + i % 17] = a;
+  }
+  if (tid < 8 * NT) {
+    float v = red_m[0][tid];
+#pragma unroll
+    for (int w2 = 1; w2 < 8; ++w2) v = fmaxf(v, red_m[w2][tid]);
+    part[tid * 18 + 17] = v;
+  }
+  __threadfence();
+  __syncthreads();
+  if (tid == 0) {
+    const int tk = atomicAdd(ticket + box, 1);
+    last = (tk == T2I_SPLITS - 1);
+    if (last) ticket[box] = 0;  // ready for the next launch
+  }
+  __syncthreads();
+  if (!last) return;
+  __threadfence();
+  const float* pb = partial + (size_t)box * T2I_SPLITS * T2I_PART;
+  for (int i = tid; i < 8 * NT * 16; i += 256) {
+    const int ht = i >> 4, d = i & 15;  // ht = head * NT + token
+    float M = -INFINITY;
+#pragma unroll
+    for (int sp = 0; sp < T2I_SPLITS; ++sp) M = fmaxf(M, __ldcg(pb + sp * T2I_PART + ht * 18 + 17));
     float a = 0.f, ls = 0.f;
 #pragma unroll
-    for (int w2 = 0; w2 < 8; ++w2) { a += red[w2][t * 17 + d]; ls += red[w2][t * 17 + 16]; }
-    out[(size_t)box * NT * 128 + t * 128 + h * 16 + d] = a / ls;
+    for (int sp = 0; sp < T2I_SPLITS; ++sp) {
+      const float* pp = pb + sp * T2I_PART + ht * 18;
+      const float w = exp2f(__ldcg(pp + 17) - M);
+      a += __ldcg(pp + d) * w;
+      ls += __ldcg(pp + 16) * w;
+    }
+    const int hh = ht / NT, t = ht % NT;
+    out[(size_t)box * NT * 128 + t * 128 + hh * 16 + d] = a / ls;
   }
 }
 
+// partial: boxes * T2I_SPLITS * T2I_PART floats of scratch; ticket: boxes ints, zero before the first launch (the
+// kernel leaves them zero).
 int launch_decoder_t2i(const float* q, const float* kv, long long box_stride, int ld, const int* box_img, float* out,
-                       int boxes, cudaStream_t st) {
-  decoder_t2i_kernel<<<boxes * 8, 256, 0, st>>>(q, kv, box_stride, ld, box_img, out);
+                       float* partial, int* ticket, int boxes, cudaStream_t st) {
+  decoder_t2i_kernel<<<dim3(T2I_SPLITS, boxes), 256, 0, st>>>(q, kv, box_stride, ld, box_img, out, partial, ticket);
   CUDA_TRY(cudaGetLastError());
   return 0;
 }
+
+size_t decoder_t2i_scratch_floats(int boxes) { return (size_t)boxes * T2I_SPLITS * T2I_PART; }
 
 // ------------------------------------------------------------------------------------------------ image -> token
 // Every image token attends to the 7 tokens (8 heads x 16). q: column `qcol` of the kvq rows (stride ld, box_stride 0

@@ -46,7 +46,8 @@ struct BoxSegments {
 
 int launch_decoder_tokens(const DecWeights& w, const DecState& s, int boxes, int phase, int layer, cudaStream_t st);
 int launch_decoder_t2i(const float* q, const float* kv, long long box_stride, int ld, const int* box_img, float* out,
-                       int boxes, cudaStream_t st);
+                       float* partial, int* ticket, int boxes, cudaStream_t st);
+size_t decoder_t2i_scratch_floats(int boxes);  // floats of `partial`; `ticket` is `boxes` ints, zeroed once
 int launch_decoder_i2t(const float* qsrc, long long box_stride, int ld, int qcol, const int* box_img, const float* kv,
                        float* out, int boxes, cudaStream_t st);
 int launch_decoder_keys0(const float* emb, const float* nomask, float* keys, int B, cudaStream_t st);

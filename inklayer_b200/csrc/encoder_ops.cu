@@ -154,18 +154,34 @@ int launch_layernorm_bf16(const float* x, const float* w, const float* b, void* 
 // In a windowed block the grid is zero-padded 64 -> 70 after norm1 (SA/modeling/image_encoder.py:258-259), so the
 // qkv of a padded token is exactly the qkv bias.  The qkv GEMM stores real tokens in window order; this fills the
 // rows of the padded tokens of that matrix ([B*25][196][3D] bf16) with bf16(bias).
+// One block = 4 of the 804 padded tokens of an image (y >= 64 or x >= 64 on the 70x70 grid); a thread converts 8 bias
+// values once and stores them (16 bytes) into the 4 rows.
 __global__ void __launch_bounds__(128) fill_pad_rows_kernel(__nv_bfloat16* __restrict__ qkv, const float* __restrict__ bias,
                                                             int cols) {
-  const int r = blockIdx.x;              // row of the window-ordered matrix
-  const int win = (r / 196) % 25, t = r % 196;
-  const int y = (win / 5) * 14 + t / 14, x = (win % 5) * 14 + t % 14;
-  if (y < 64 && x < 64) return;
-  __nv_bfloat162* o = reinterpret_cast<__nv_bfloat162*>(qkv + (size_t)r * cols);
-  for (int c = threadIdx.x; c < cols / 2; c += blockDim.x) o[c] = __floats2bfloat162_rn(bias[2 * c], bias[2 * c + 1]);
+  const int b = blockIdx.y, p0 = blockIdx.x * 4;
+  size_t row[4];
+#pragma unroll
+  for (int i = 0; i < 4; ++i) {
+    const int p = p0 + i;  // 0..803: the 6 bottom rows of the padded grid (420 tokens), then the 6 right columns of the rest
+    const int y = p < 420 ? 64 + p / 70 : (p - 420) / 6, x = p < 420 ? p % 70 : 64 + (p - 420) % 6;
+    const int win = (y / 14) * 5 + x / 14, t = (y % 14) * 14 + x % 14;
+    row[i] = ((size_t)(b * 25 + win) * 196 + t) * (size_t)cols;
+  }
+  for (int c = threadIdx.x * 8; c < cols; c += blockDim.x * 8) {
+    const float4 f0 = *reinterpret_cast<const float4*>(bias + c), f1 = *reinterpret_cast<const float4*>(bias + c + 4);
+    __nv_bfloat162 h0 = __floats2bfloat162_rn(f0.x, f0.y), h1 = __floats2bfloat162_rn(f0.z, f0.w);
+    __nv_bfloat162 h2 = __floats2bfloat162_rn(f1.x, f1.y), h3 = __floats2bfloat162_rn(f1.z, f1.w);
+    uint4 pk;
+    pk.x = *reinterpret_cast<uint32_t*>(&h0); pk.y = *reinterpret_cast<uint32_t*>(&h1);
+    pk.z = *reinterpret_cast<uint32_t*>(&h2); pk.w = *reinterpret_cast<uint32_t*>(&h3);
+#pragma unroll
+    for (int i = 0; i < 4; ++i) *reinterpret_cast<uint4*>(qkv + row[i] + c) = pk;
+  }
 }
 
 int launch_fill_pad_rows(void* qkv, const float* bias, int B, int cols, cudaStream_t st) {
-  fill_pad_rows_kernel<<<B * 25 * 196, 128, 0, st>>>(static_cast<__nv_bfloat16*>(qkv), bias, cols);
+  if (cols % 8 != 0) return set_error("fill_pad_rows: cols=%d must be a multiple of 8", cols);
+  fill_pad_rows_kernel<<<dim3(804 / 4, B), 128, 0, st>>>(static_cast<__nv_bfloat16*>(qkv), bias, cols);
   CUDA_TRY(cudaGetLastError());
   return 0;
 }

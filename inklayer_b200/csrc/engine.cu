@@ -518,6 +518,9 @@ int decode_chunk(inksam_handle* h, const float* keys0, const float* kvq0, char* 
   s.attn_t2i = reinterpret_cast<float*>(take((size_t)n * 7 * 128 * 4));
   s.kv_i2t = reinterpret_cast<float*>(take((size_t)n * 2 * 7 * 128 * 4));
   s.hyper = reinterpret_cast<float*>(take((size_t)n * 32 * 4));
+  float* t2i_part = reinterpret_cast<float*>(take(decoder_t2i_scratch_floats(n) * 4));
+  int* t2i_ticket = reinterpret_cast<int*>(take((size_t)n * 4));
+  CUDA_TRY(cudaMemsetAsync(t2i_ticket, 0, (size_t)n * 4, st));
   s.iou = iou + k0;
   low += (size_t)k0 * 65536;
   const int* bimg = box_img + k0;
@@ -526,7 +529,7 @@ int decode_chunk(inksam_handle* h, const float* keys0, const float* kvq0, char* 
   auto tokens = [&](int phase, int layer) { ++h->launches; return launch_decoder_tokens(h->dec, s, n, phase, layer, st); };
   auto t2i = [&](const float* kv, long long stride, int ld, const int* bi) {
     ++h->launches;
-    return launch_decoder_t2i(s.q_t2i, kv, stride, ld, bi, s.attn_t2i, n, st);
+    return launch_decoder_t2i(s.q_t2i, kv, stride, ld, bi, s.attn_t2i, t2i_part, t2i_ticket, n, st);
   };
   auto i2t = [&](const float* q, long long stride, const int* bi) {
     ++h->launches;
@@ -656,7 +659,8 @@ extern "C" int inksam_decode_batch(inksam_handle* h, const float* embeddings, in
   const size_t sz_idx = align_up((size_t)K * 4);
   const size_t shared_bytes = sz_keys0 + sz_kvq0 + sz_idx;
   const size_t chunk_bytes = align_up((size_t)nc * 4096 * 256 * 4) + align_up((size_t)nc * 4096 * 384 * 4) +
-                             align_up((size_t)nc * 4096 * 128 * 4) + 8 * align_up((size_t)nc * 7 * 256 * 4);
+                             align_up((size_t)nc * 4096 * 128 * 4) + 8 * align_up((size_t)nc * 7 * 256 * 4) +
+                             align_up(decoder_t2i_scratch_floats(nc) * 4) + align_up((size_t)nc * 4);
   INK_TRY(grow(&h->dec_ws, &h->dec_ws_bytes, shared_bytes + chunk_bytes));
   char* ws = static_cast<char*>(h->dec_ws);
   float* keys0 = reinterpret_cast<float*>(ws);

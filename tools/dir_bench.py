@@ -34,6 +34,7 @@ def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--sketches", type=int, default=4096)
     ap.add_argument("--model", default="vit_h")
+    ap.add_argument("--hw", type=int, nargs=2, default=[1024, 1024], help="sketch size (H W); other than 1024 exercises the device resize")
     args = ap.parse_args()
     rank, world, local = (int(os.environ.get(k, d)) for k, d in (("RANK", "0"), ("WORLD_SIZE", "1"), ("LOCAL_RANK", "0")))
     torch.cuda.set_device(local)
@@ -49,7 +50,7 @@ def main():
     def sketch(i):
         k = i % POOL
         if k not in pool:
-            pool[k] = synthetic_sketch(k)
+            pool[k] = synthetic_sketch(k, args.hw[0], args.hw[1])
         return pool[k]
 
     for i in mine[:POOL * world]:
@@ -57,7 +58,7 @@ def main():
 
     def feed(idx):
         for g in batched(idx, BATCH):
-            yield [sketch(i) for i in g], [synthetic_boxes(i, BOXES) for i in g]
+            yield [sketch(i) for i in g], [synthetic_boxes(i, BOXES, args.hw[0], args.hw[1]) for i in g]
 
     for _ in seg.segment_stream(feed(mine[:3 * BATCH])):   # warm-up: 3 batches
         pass
@@ -76,7 +77,7 @@ def main():
         dist.all_reduce(cnt, op=dist.ReduceOp.SUM)
     if rank == 0:
         print(json.dumps({"config": "4: --dir over synthetic sketches sharded by image", "model": args.model,
-                          "sketches": args.sketches, "n_gpus": world, "boxes_per_sketch": BOXES, "masks": int(cnt.item()),
+                          "sketches": args.sketches, "sketch_hw": args.hw, "n_gpus": world, "boxes_per_sketch": BOXES, "masks": int(cnt.item()),
                           "seconds": float(dt.item()), "sketches_per_s": args.sketches / float(dt.item()),
                           "h2d_bytes": seg.h2d_bytes, "d2h_bytes": seg.d2h_bytes, "host_cores": os.cpu_count()}))
     if world > 1:
