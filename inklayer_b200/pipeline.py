@@ -117,7 +117,7 @@ class SketchSegmenter:
             self._s_run.wait_event(slot.ev_in)
             for i, off, H, W in raw:
                 sam.resize_longest_side(slot.dev_raw[off:off + H * W * 3].view(H, W, 3), out=slot.dev_img[i])
-            feats = sam.encode(slot.dev_img[:B], in_sizes)
+            feats = sam.encode(slot.dev_img[:B], in_sizes, graph=True)  # per-slot input buffer: replayed from a CUDA graph
             counts = [len(t) for t in tbs]
             splits = list(torch.split(db, counts)) if db.numel() else [db[:0] for _ in tbs]
             _, _, _, offs = sam.decode_batch(feats, splits, in_sizes, sizes, masks_out=slot.dev_masks)

@@ -36,6 +36,10 @@ class Sam:
         self.device = torch.device("cpu")
         self._sd: Optional[Dict[str, torch.Tensor]] = None
         self._handle: Optional[ctypes.c_void_p] = None
+        self._graphs: dict = {}        # encode() CUDA graphs: key -> (graph, output, input, kernel launches per replay)
+        self._graph_seen: dict = {}
+        self._graph_launches = 0       # kernels launched by graph replays (the library counts stream launches only)
+        self._profiling = False
 
     # ------------------------------------------------------------------ weights
     def load_state_dict(self, state_dict: Dict[str, torch.Tensor], strict: bool = True) -> None:
@@ -90,6 +94,8 @@ class Sam:
         return self.to(torch.device("cuda", torch.cuda.current_device() if index is None else index))
 
     def _upload(self) -> None:
+        self._graphs.clear()  # captured graphs hold pointers into the previous weight set
+        self._graph_seen.clear()
         lib = _lib.load()
         with torch.cuda.device(self.device):
             st = _stream(self.device)
@@ -101,6 +107,8 @@ class Sam:
             torch.cuda.current_stream(self.device).synchronize()
 
     def _destroy(self) -> None:
+        self._graphs.clear()
+        self._graph_seen.clear()
         if self._handle is not None:
             _lib.load().inksam_destroy(self._handle)
             self._handle = None
@@ -118,11 +126,12 @@ class Sam:
 
     @property
     def launch_count(self) -> int:
-        return int(_lib.load().inksam_launch_count(self._require()))
+        return int(_lib.load().inksam_launch_count(self._require())) + self._graph_launches
 
     def profile(self, on: bool) -> None:
         """Start (and reset) / stop per-category CUDA-event timing of the library's launches."""
         _lib.check(_lib.load().inksam_profile_enable(self._require(), 1 if on else 0))
+        self._profiling = bool(on)  # per-launch events are not part of a captured graph: encode() uses stream launches
 
     def profile_read(self):
         """{category: (ms, work, launches)} since profile(True); waits for the recorded events."""
@@ -133,11 +142,15 @@ class Sam:
 
     # ------------------------------------------------------------------ compute (C ABI)
     @torch.no_grad()
-    def encode(self, images: torch.Tensor, sizes: Optional[Sequence[Tuple[int, int]]] = None) -> torch.Tensor:
+    def encode(self, images: torch.Tensor, sizes: Optional[Sequence[Tuple[int, int]]] = None, graph: bool = False) -> torch.Tensor:
         """Sam.preprocess + image encoder (modeling/sam.py:164-174, image_encoder.py:106-116) for a batch.
         images: uint8 [B,h,w,3] (HWC) or float32 [B,3,h,w] (values 0..255) on this device, long side <= 1024;
-        `sizes` optionally gives each image's valid (h, w) inside the container.  Returns float32 [B,256,64,64]."""
-        h = self._require()
+        `sizes` optionally gives each image's valid (h, w) inside the container.  Returns float32 [B,256,64,64].
+
+        graph=True: the ~260 kernel launches of the encoder are replayed from a CUDA graph captured for this input
+        buffer (same data pointer, batch and sizes; captured the second time the combination is seen).  The result is
+        then a buffer owned by the graph, valid until the next encode of the same input buffer on this stream."""
+        self._require()
         if images.device != self.device:
             raise RuntimeError(f"images are on {images.device}, model on {self.device}")
         images = images.contiguous()
@@ -158,10 +171,36 @@ class Sam:
         for i in range(B):
             sh, sw = (hh, ww) if sizes is None else sizes[i]
             hw[2 * i], hw[2 * i + 1] = int(sh), int(sw)
+
+        def run(out: torch.Tensor) -> None:
+            with torch.cuda.device(self.device):
+                _lib.check(_lib.load().inksam_encode(self._require(), _ptr(images), dtype, B, hw, img_stride, row_pitch, plane,
+                                                     _ptr(out), _stream(self.device)))
+
+        if graph and not self._profiling:
+            key = (images.data_ptr(), dtype, B, hh, ww, tuple(hw))
+            hit = self._graphs.get(key)
+            if hit is not None:
+                hit[0].replay()
+                self._graph_launches += hit[3]
+                return hit[1]
+            self._graph_seen[key] = self._graph_seen.get(key, 0) + 1
+            if self._graph_seen[key] >= 2 and len(self._graphs) < 16:
+                out = torch.empty((B, self.cfg.out_chans, 64, 64), dtype=torch.float32, device=self.device)
+                n0 = int(_lib.load().inksam_launch_count(self._require()))
+                run(out)  # workspaces are grown outside the capture
+                per_replay = int(_lib.load().inksam_launch_count(self._require())) - n0
+                g = torch.cuda.CUDAGraph()
+                # thread_local: SketchSegmenter's hand-off thread may be waiting on events / copying while this captures
+                with torch.cuda.graph(g, capture_error_mode="thread_local"):
+                    run(out)
+                self._graphs[key] = (g, out, images, per_replay)  # the input buffer stays alive with its graph
+                self._graph_launches -= per_replay  # the capture pass counted launches that did not execute
+                g.replay()
+                self._graph_launches += per_replay
+                return out
         out = torch.empty((B, self.cfg.out_chans, 64, 64), dtype=torch.float32, device=self.device)
-        with torch.cuda.device(self.device):
-            _lib.check(_lib.load().inksam_encode(h, _ptr(images), dtype, B, hw, img_stride, row_pitch, plane, _ptr(out),
-                                                 _stream(self.device)))
+        run(out)
         return out
 
     @torch.no_grad()
