@@ -9,7 +9,7 @@ import os
 from ctypes import POINTER, c_char_p, c_float, c_int, c_int64, c_longlong, c_size_t, c_void_p
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(_HERE, "libinksam.so")
+LIB_PATH = os.environ.get("INKSAM_LIB", os.path.join(_HERE, "libinksam.so"))  # override: A/B builds of the library
 
 
 class InksamConfig(ctypes.Structure):

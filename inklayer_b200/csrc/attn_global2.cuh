@@ -95,6 +95,7 @@ attn_global2_kernel(const __grid_constant__ CUtensorMap tm64, const __grid_const
   __syncthreads();
   tc_fence_after();
   const uint32_t tmem_base = *tmem_slot_ptr;
+  pdl_launch_dependents();  // the proj GEMM (launched with PDL) may run its prologue under this kernel's tail
   auto S_COL = [](int g, int buf) { return (uint32_t)(128 * g + 64 * buf); };
   auto O_COL = [](int g) { return (uint32_t)(256 + 128 * g); };
 

@@ -75,6 +75,7 @@ attn_window2_kernel(const __grid_constant__ CUtensorMap tq64, const __grid_const
   __syncthreads();
   tc_fence_after();
   const uint32_t tmem_base = *tmem_slot_ptr;
+  pdl_launch_dependents();  // the proj GEMM (launched with PDL) may run its prologue under this kernel's tail
 
   // The CTA walks (window, head) pairs blockIdx.x, blockIdx.x + gridDim.x, ...; each pair is two consecutive items
   // (row tiles mt = 0, 1) that share ONE load of the window's K and V.  num_items = 2 * pairs.

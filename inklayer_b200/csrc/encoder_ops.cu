@@ -1,6 +1,7 @@
 // HBM-bound helper kernels of the image encoder: pixel normalisation + patch gather, LayerNorm -> bf16,
 // fp32 -> bf16 cast, and the bias rows of padded window tokens.
 #include "common.h"
+#include "ptx.cuh"
 
 namespace inksam {
 
@@ -82,6 +83,7 @@ template <int MAXC>
 __global__ void __launch_bounds__(256) layernorm_bf16_kernel(const float* __restrict__ x, const float* __restrict__ w,
                                                              const float* __restrict__ bsh, __nv_bfloat16* __restrict__ out,
                                                              int M, int D, float eps, int plain) {
+  pdl_launch_dependents();  // the consuming GEMM (launched with PDL) may run its prologue under this kernel's last wave
   const int row = blockIdx.x * 8 + (threadIdx.x >> 5);
   const int lane = threadIdx.x & 31;
   if (row >= M) return;

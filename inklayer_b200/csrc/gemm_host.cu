@@ -101,13 +101,17 @@ static int launch_one(const CUtensorMap& tA, const CUtensorMap& tB, const CUtens
   cfg.blockDim = dim3(384);
   cfg.dynamicSmemBytes = C::SMEM_BYTES;
   cfg.stream = st;
-  cudaLaunchAttribute attr[1];
+  cudaLaunchAttribute attr[2];
   attr[0].id = cudaLaunchAttributeClusterDimension;
   attr[0].val.clusterDim.x = CG;
   attr[0].val.clusterDim.y = 1;
   attr[0].val.clusterDim.z = 1;
+  // programmatic dependent launch: the prologue may overlap the tail of the preceding kernel of the stream; the kernel
+  // waits (griddepcontrol.wait) before it touches global data
+  attr[1].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+  attr[1].val.programmaticStreamSerializationAllowed = 1;
   cfg.attrs = attr;
-  cfg.numAttrs = 1;
+  cfg.numAttrs = 2;
   // The tile loop is statically strided over the resident clusters, so the grid must not exceed what is
   // co-resident: CTA pairs need both SMs of a TPC, and not every SM of the 148 can be paired on every part.
   static int max_clusters = 0;

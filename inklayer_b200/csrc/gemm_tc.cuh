@@ -130,6 +130,10 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
   if constexpr (CG == 2) cluster_sync_all(); else __syncthreads();
   tc_fence_after();
   const uint32_t tmem_base = *tmem_slot_ptr;
+  // PDL: everything above (barrier init, TMEM allocation, descriptor prefetch) touched no global data and may have
+  // run under the tail of the preceding kernel; from here on its results are needed (and its inputs may be overwritten)
+  pdl_grid_dep_wait();
+  pdl_launch_dependents();
 
   if (warp == 0) {
     // ------------------------------------------------------------ TMA producer

@@ -289,6 +289,13 @@ __device__ __forceinline__ float ex2_approx(float x) {
   return y;
 }
 
+// ---------------------------------------------------------------- programmatic dependent launch (PDL)
+// launch_dependents: the next kernel of the stream (if launched with programmatic stream serialization) may start its
+// prologue once every CTA of this grid has called this or exited.  grid_dep_wait: returns when the preceding grid has
+// completed and its memory is visible; a no-op for a kernel launched without the attribute.
+__device__ __forceinline__ void pdl_launch_dependents() { asm volatile("griddepcontrol.launch_dependents;" ::: "memory"); }
+__device__ __forceinline__ void pdl_grid_dep_wait() { asm volatile("griddepcontrol.wait;" ::: "memory"); }
+
 // ---------------------------------------------------------------- TMA store (shared -> global), bulk async-groups
 __device__ __forceinline__ void tma_store_2d(const void* tmap, uint32_t src_smem, int c0, int c1) {
   asm volatile("cp.async.bulk.tensor.2d.global.shared::cta.bulk_group [%0, {%2, %3}], [%1];" ::"l"(tmap), "r"(src_smem),
