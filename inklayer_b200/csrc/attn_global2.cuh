@@ -13,8 +13,8 @@
 // P(t) (bf16) is written back over the first 32 columns of S(t).  The prologue borrows all 512 columns for the
 // rel-pos products T_h / T_w of both tiles (T[q][r] = q . rel_pos[r] on the UNSCALED q, image_encoder.py:234,354-355)
 // and the K ring for the tables.
-// Softmax follows attn_tc.cuh: exp2 with a fixed shift taken from the first 32 keys, exact rescale if a later key
-// exceeds it by 2^32 (cold path).
+// Softmax follows attn_tc.cuh: exp2 with a fixed shift taken from the first 32 keys, exact power-of-two rescale once
+// the running sum passes 2^32 (cold path).
 #pragma once
 #include "attn_tc.cuh"
 
@@ -44,6 +44,10 @@ attn_global2_kernel(const __grid_constant__ CUtensorMap tm64, const __grid_const
   constexpr uint32_t IDESC_S = make_idesc(1u, 128, 64);
   constexpr int NT = 32;   // key tiles of 128 (TMA / smem ring granularity)
   constexpr int NS = 64;   // sub-tiles of 64 keys (MMA / softmax granularity)
+#ifndef INKSAM_KPOLY
+#define INKSAM_KPOLY 8
+#endif
+  constexpr int kPoly = INKSAM_KPOLY;  // keys per sub-tile whose exp2 runs on the FMA pipe (even, <= 32)
 
   extern __shared__ uint8_t smem_raw[];
   const uint32_t smem_base = (smem_u32(smem_raw) + 1023u) & ~1023u;
@@ -193,7 +197,7 @@ attn_global2_kernel(const __grid_constant__ CUtensorMap tm64, const __grid_const
 
     mbar_wait(bar_tdone, 0);
     tc_fence_after();
-    float bW[64];  // bias_w[kw] * log2e for this query
+    uint64_t bW2[32];  // (bias_w[2j], bias_w[2j+1]) * log2e for this query, packed for f32x2 arithmetic
     {
       float t[128];  // T_w row; indexed per thread below -> lives in local memory
       uint32_t v[32];
@@ -206,7 +210,7 @@ attn_global2_kernel(const __grid_constant__ CUtensorMap tm64, const __grid_const
       }
       const float* tp = t + qw + 63;
 #pragma unroll
-      for (int i = 0; i < 64; ++i) bW[i] = tp[-i] * kLog2e;  // T_w[q][qw - kw + 63]
+      for (int i = 0; i < 64; i += 2) bW2[i >> 1] = f2_pack(tp[-i] * kLog2e, tp[-i - 1] * kLog2e);  // T_w[q][qw - kw + 63]
       // T_h[q][qh - kh + 63]: qh is uniform over the warp, so the 64 needed columns start at column qh for all lanes
       uint32_t h0[32], h1[32];
       tmem_ld_32x32(lane_base + 256 * g + (uint32_t)qh, h0);
@@ -223,7 +227,9 @@ attn_global2_kernel(const __grid_constant__ CUtensorMap tm64, const __grid_const
     if (lane == 0) mbar_arrive(bar_tread);
 
     float m_used = 0.f, l = 0.f;
+    uint64_t l2 = f2_pack(0.f, 0.f);  // two partial row sums (even / odd keys), folded into l after every sub-tile
     const float c1 = a.c1;
+    const uint64_t c12 = f2_pack(c1, c1);
     const uint32_t o_addr = lane_base + O_COL(g);
 #pragma unroll 1
     for (int t = 0; t < NS; ++t) {
@@ -240,39 +246,58 @@ attn_global2_kernel(const __grid_constant__ CUtensorMap tm64, const __grid_const
       if (t == 0) {  // shift = max over the first 32 keys
         float mx = -INFINITY;
 #pragma unroll
-        for (int i = 0; i < 32; ++i) mx = fmaxf(mx, fmaf(__uint_as_float(v0[i]), c1, bW[i] + bh));
+        for (int i = 0; i < 32; i += 2) {
+          float b0, b1;
+          f2_unpack(bW2[i >> 1], b0, b1);
+          mx = fmaxf(mx, fmaxf(fmaf(__uint_as_float(v0[i]), c1, b0 + bh), fmaf(__uint_as_float(v0[i + 1]), c1, b1 + bh)));
+        }
         m_used = mx;
       }
       const float bb = bh - m_used;
-      float tmax = -INFINITY;
+      const uint64_t bb2 = f2_pack(bb, bb);
       uint32_t pk[32];
+      // two keys per instruction: x = s * c1 + (bias_w + bias_h - shift) as fma.rn.f32x2 / add.rn.f32x2
 #pragma unroll
       for (int i = 0; i < 32; i += 2) {
-        const float x0 = fmaf(__uint_as_float(v0[i]), c1, bW[i] + bb);
-        const float x1 = fmaf(__uint_as_float(v0[i + 1]), c1, bW[i + 1] + bb);
-        tmax = fmaxf(tmax, fmaxf(x0, x1));
+        float x0, x1;
+        f2_unpack(f2_fma(f2_pack(__uint_as_float(v0[i]), __uint_as_float(v0[i + 1])), c12, f2_add(bW2[i >> 1], bb2)), x0, x1);
         const float p0 = ex2_approx(fminf(x0, 120.f)), p1 = ex2_approx(fminf(x1, 120.f));
-        l += p0 + p1;
+        l2 = f2_add(l2, f2_pack(p0, p1));
         pk[i >> 1] = pack_bf16x2(p0, p1);
       }
+      // The MUFU pipe (16 ex2 per clock and SM) is the busiest unit of this kernel: kPoly of the 64 keys of a sub-tile
+      // take their exp2 from an FMA-pipe polynomial instead.
 #pragma unroll
       for (int i = 0; i < 32; i += 2) {
-        const float x0 = fmaf(__uint_as_float(v1[i]), c1, bW[32 + i] + bb);
-        const float x1 = fmaf(__uint_as_float(v1[i + 1]), c1, bW[32 + i + 1] + bb);
-        tmax = fmaxf(tmax, fmaxf(x0, x1));
-        const float p0 = ex2_approx(fminf(x0, 120.f)), p1 = ex2_approx(fminf(x1, 120.f));
-        l += p0 + p1;
+        float x0, x1;
+        f2_unpack(f2_fma(f2_pack(__uint_as_float(v1[i]), __uint_as_float(v1[i + 1])), c12, f2_add(bW2[16 + (i >> 1)], bb2)), x0, x1);
+        float p0, p1;
+        if (i >= 32 - kPoly) {
+          f2_unpack(f2_exp2_poly(f2_pack(fmaxf(fminf(x0, 120.f), -126.f), fmaxf(fminf(x1, 120.f), -126.f))), p0, p1);
+        } else {
+          p0 = ex2_approx(fminf(x0, 120.f)); p1 = ex2_approx(fminf(x1, 120.f));
+        }
+        l2 = f2_add(l2, f2_pack(p0, p1));
         pk[16 + (i >> 1)] = pack_bf16x2(p0, p1);
+      }
+      {
+        float la, lb;
+        f2_unpack(l2, la, lb);
+        l += la + lb;
+        l2 = f2_pack(0.f, 0.f);
       }
       tmem_st_32x32(s_addr, pk);  // P(t) over the first 32 columns of S(t), all of which have been read
       tmem_st_wait();
       tc_fence_before();
       __syncwarp();
       if (lane == 0) mbar_arrive(bar_pready(g, buf));
-      const bool need = tmax > 32.f;
+      // The running sum bounds every probability so far: once it passes 2^32 the shift moves up by log2(l) (an exact
+      // power-of-two rescale of l and O), so no per-element maximum has to be tracked in the hot loop.
+      const bool need = l > 4294967296.f;
       if (__any_sync(0xffffffffu, need)) {  // exact but cold: move the shift up and rescale the accumulator
         mbar_wait(bar_pvdone(g, buf), par);  // PV(t) has been accumulated with the old shift
         tc_fence_after();
+        const float tmax = need ? (float)((int)((__float_as_uint(l) >> 23) & 0xffu) - 127) : 0.f;  // floor(log2 l)
         const float alpha = need ? ex2_approx(-tmax) : 1.f;
         if (need) m_used += tmax;
         l *= alpha;

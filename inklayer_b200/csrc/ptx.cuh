@@ -289,6 +289,48 @@ __device__ __forceinline__ float ex2_approx(float x) {
   return y;
 }
 
+// ---------------------------------------------------------------- packed fp32x2 arithmetic (sm_100: two IEEE fp32 lanes per op)
+__device__ __forceinline__ uint64_t f2_pack(float lo, float hi) {
+  uint64_t r;
+  asm("mov.b64 %0, {%1, %2};" : "=l"(r) : "f"(lo), "f"(hi));
+  return r;
+}
+__device__ __forceinline__ void f2_unpack(uint64_t v, float& lo, float& hi) {
+  asm("mov.b64 {%0, %1}, %2;" : "=f"(lo), "=f"(hi) : "l"(v));
+}
+__device__ __forceinline__ uint64_t f2_fma(uint64_t a, uint64_t b, uint64_t c) {
+  uint64_t d;
+  asm("fma.rn.f32x2 %0, %1, %2, %3;" : "=l"(d) : "l"(a), "l"(b), "l"(c));
+  return d;
+}
+__device__ __forceinline__ uint64_t f2_add(uint64_t a, uint64_t b) {
+  uint64_t d;
+  asm("add.rn.f32x2 %0, %1, %2;" : "=l"(d) : "l"(a), "l"(b));
+  return d;
+}
+
+// exp2 of two values on the FMA / ALU pipes (no MUFU): Cody-Waite split x = n + f, f in [-0.5, 0.5], 2^f by a cubic
+// (relative error 8e-5, far below the bf16 rounding of the probabilities it feeds), 2^n by an exponent add.
+// x must lie in [-126, 126].
+__device__ __forceinline__ uint64_t f2_exp2_poly(uint64_t x) {
+  const uint64_t magic = f2_pack(12582912.f, 12582912.f);          // 1.5 * 2^23: the integer part lands in the mantissa
+  const uint64_t neg_magic = f2_pack(-12582912.f, -12582912.f);
+  const uint64_t t = f2_add(x, magic);
+  const uint64_t n = f2_add(t, neg_magic);                          // round(x)
+  uint64_t f;
+  asm("sub.rn.f32x2 %0, %1, %2;" : "=l"(f) : "l"(x), "l"(n));
+  // least-squares cubic for 2^f on [-0.5, 0.5] at Chebyshev nodes, relative error <= 7.8e-5
+  uint64_t p = f2_fma(f2_pack(0.05508868f, 0.05508868f), f, f2_pack(0.24260405f, 0.24260405f));
+  p = f2_fma(p, f, f2_pack(0.69327624f, 0.69327624f));
+  p = f2_fma(p, f, f2_pack(0.99992894f, 0.99992894f));
+  float t0, t1, p0, p1;
+  f2_unpack(t, t0, t1);
+  f2_unpack(p, p0, p1);
+  const float r0 = __uint_as_float(__float_as_uint(p0) + (__float_as_uint(t0) << 23));
+  const float r1 = __uint_as_float(__float_as_uint(p1) + (__float_as_uint(t1) << 23));
+  return f2_pack(r0, r1);
+}
+
 // ---------------------------------------------------------------- programmatic dependent launch (PDL)
 // launch_dependents: the next kernel of the stream (if launched with programmatic stream serialization) may start its
 // prologue once every CTA of this grid has called this or exited.  grid_dep_wait: returns when the preceding grid has

@@ -49,6 +49,32 @@ def test_global_attention(hd, heads, B):
     assert rel_err(out, ref) < 1.5e-2
 
 
+@pytest.mark.parametrize("hd,peak_at", [(80, 3000), (64, 70), (80, 4095)])
+def test_global_attention_late_peak_rescales(hd, peak_at):
+    """The lazy softmax shift comes from the first 32 keys; a much later key whose score is ~40 log2 units above it
+    (probability ratio 2^40) must trigger the exact rescale of the running sum and of the O accumulator in TMEM."""
+    lib = _lib.load()
+    heads, B = 2, 1
+    g = torch.Generator().manual_seed(7 + hd + peak_at)
+    D = heads * hd
+    u = torch.ones(hd) / hd ** 0.5
+    t = torch.randn(3, B, heads, 4096, hd, generator=g) * 1.0
+    t[0] += 5.0 * u                       # every query has a component along u
+    t[1, :, :, peak_at] += 50.0 * u       # one key far along u: score about 5 * 50 / sqrt(hd) nats above the rest
+    qkv = t.permute(1, 3, 0, 2, 4).reshape(B * 4096, 3 * D).to(torch.bfloat16)
+    rel_h = (torch.randn(127, hd, generator=g) * 0.1).to(torch.bfloat16).float()
+    rel_w = (torch.randn(127, hd, generator=g) * 0.1).to(torch.bfloat16).float()
+    out = torch.zeros(B * 4096, D, dtype=torch.bfloat16, device="cuda")
+    _lib.check(lib.inksam_op_attention(0, ptr(qkv.cuda()), ptr(rel_table(rel_h, rel_w, 256)), ptr(out), B, heads, hd, stream()))
+    torch.cuda.synchronize()
+    tt = qkv.float().cuda().reshape(B, 4096, 3, heads, hd).permute(2, 0, 3, 1, 4).reshape(3, B * heads, 4096, hd)
+    ref = ref_attention(tt[0], tt[1], tt[2], rel_h.cuda(), rel_w.cuda(), 64)
+    ref = ref.reshape(B, heads, 4096, hd).permute(0, 2, 1, 3).reshape(B * 4096, D)
+    assert torch.isfinite(out.float()).all()
+    assert rel_rms(out, ref) < 1e-2
+    assert rel_err(out, ref) < 1.5e-2
+
+
 @pytest.mark.parametrize("hd,heads,B", [(64, 2, 1), (80, 2, 1), (80, 3, 2)])
 def test_window_attention(hd, heads, B):
     """Windowed blocks: 14x14 windows over the zero-padded 70x70 grid; padded tokens carry the qkv bias and are NOT
