@@ -51,6 +51,24 @@ int inksam_op_attention(int windowed, const void* qkv, const void* rel, void* ou
 /* nn.LayerNorm over the last dim (fp32 in, bf16 out); plain != 0 only casts. image_encoder.py:168,180. */
 int inksam_op_layernorm(const float* x, const float* w, const float* b, void* out, int M, int D, float eps, int plain, void* stream);
 
+/* LayerNorm folded into the GEMMs either side of it (the encoder blocks' norm1 -> qkv and norm2 -> lin1,
+ * image_encoder.py:180-197):   LN(x) W^T + b == rstd * (x (gamma o W)^T) - rstd * mean * colsum(gamma o W) + (b + W beta).
+ *   inksam_op_fold_ln_weights: W fp32 [N][K] -> w_out bf16 [N][K] = gamma o W, colsum [N] (of the rounded values),
+ *                              bias_out [N] = bias + W beta.
+ *   inksam_op_row_stats_bf16:  x fp32 [M][D] -> out bf16 [M][D] (plain cast) and stats [M][2] = (sum, sum of squares).
+ *   inksam_op_gemm_fold:       CTA-pair bf16 GEMM, BN 256.  epi 2 (bias + fp32 residual): also writes stats_out
+ *                              [M][inksam_op_gemm_stats_partials(N)][2] and the bf16 copy xb_out [M][ldo] of its output
+ *                              (both, or both null for the plain epilogue).  epi 0 / 1 (bf16 out, optional GELU): A is the raw bf16 x, W / colsum /
+ *                              bias come from inksam_op_fold_ln_weights, stats_in [M][stats_np][2] are partials of the
+ *                              rows of A over its K columns. */
+int inksam_op_fold_ln_weights(const float* W, const float* gamma, const float* beta, const float* bias, void* w_out,
+                              float* colsum, float* bias_out, int N, int K, void* stream);
+int inksam_op_row_stats_bf16(const float* x, void* out, float* stats, int M, int D, void* stream);
+int inksam_op_gemm_stats_partials(int N);
+int inksam_op_gemm_fold(int epi, const void* A, int lda, const void* W, int ldw, int M, int N, int K, void* out, int ldo,
+                        const float* bias, const float* resid, float* stats_out, void* xb_out, const float* stats_in,
+                        const float* colsum, int stats_np, float eps, int win_remap, void* stream);
+
 /* Sam.preprocess + PatchEmbed im2col: out bf16 [B*4096][768]. hw is a HOST array. modeling/sam.py:164-174. */
 int inksam_op_patchify(const void* images, int dtype, int B, const int* hw, long long img_stride, long long row_pitch,
                        long long plane_stride, const float* mean, const float* stdv, void* out, void* stream);

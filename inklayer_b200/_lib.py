@@ -45,6 +45,11 @@ SIGNATURES = {
                                c_int, c_int, c_int, c_void_p]),
     "inksam_op_attention": (c_int, [c_int, c_void_p, c_void_p, c_void_p, c_int, c_int, c_int, c_void_p]),
     "inksam_op_layernorm": (c_int, [c_void_p, c_void_p, c_void_p, c_void_p, c_int, c_int, c_float, c_int, c_void_p]),
+    "inksam_op_fold_ln_weights": (c_int, [c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_int, c_int, c_void_p]),
+    "inksam_op_row_stats_bf16": (c_int, [c_void_p, c_void_p, c_void_p, c_int, c_int, c_void_p]),
+    "inksam_op_gemm_stats_partials": (c_int, [c_int]),
+    "inksam_op_gemm_fold": (c_int, [c_int, c_void_p, c_int, c_void_p, c_int, c_int, c_int, c_int, c_void_p, c_int, c_void_p, c_void_p,
+                                    c_void_p, c_void_p, c_void_p, c_void_p, c_int, c_float, c_int, c_void_p]),
     "inksam_op_patchify": (c_int, [c_void_p, c_int, c_int, POINTER(c_int), c_longlong, c_longlong, c_longlong,
                                    POINTER(c_float), POINTER(c_float), c_void_p, c_void_p]),
     "inksam_op_fill_pad_rows": (c_int, [c_void_p, c_void_p, c_int, c_int, c_void_p]),

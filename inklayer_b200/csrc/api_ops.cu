@@ -35,7 +35,38 @@ int inksam_op_attention(int windowed, const void* qkv, const void* rel, void* ou
 }
 
 int inksam_op_layernorm(const float* x, const float* w, const float* b, void* out, int M, int D, float eps, int plain, void* stream) {
-  return launch_layernorm_bf16(x, w, b, out, M, D, eps, plain, static_cast<cudaStream_t>(stream));
+  return launch_layernorm_bf16(x, w, b, out, M, D, eps, plain, nullptr, static_cast<cudaStream_t>(stream));
+}
+
+int inksam_op_row_stats_bf16(const float* x, void* out, float* stats, int M, int D, void* stream) {
+  if (!stats) return set_error("inksam_op_row_stats_bf16: null stats");
+  return launch_layernorm_bf16(x, nullptr, nullptr, out, M, D, 0.f, 1, stats, static_cast<cudaStream_t>(stream));
+}
+
+int inksam_op_fold_ln_weights(const float* W, const float* gamma, const float* beta, const float* bias, void* w_out,
+                              float* colsum, float* bias_out, int N, int K, void* stream) {
+  if (!W || !gamma || !beta || !bias || !w_out || !colsum || !bias_out) return set_error("inksam_op_fold_ln_weights: null argument");
+  return launch_fold_ln_weights(W, gamma, beta, bias, w_out, colsum, bias_out, N, K, static_cast<cudaStream_t>(stream));
+}
+
+int inksam_op_gemm_stats_partials(int N) { return gemm_stats_partials(N); }
+
+int inksam_op_gemm_fold(int epi, const void* A, int lda, const void* W, int ldw, int M, int N, int K, void* out, int ldo,
+                        const float* bias, const float* resid, float* stats_out, void* xb_out, const float* stats_in,
+                        const float* colsum, int stats_np, float eps, int win_remap, void* stream) {
+  if (epi != EPI_BIAS_BF16 && epi != EPI_BIAS_GELU_BF16 && epi != EPI_BIAS_RESID_F32)
+    return set_error("inksam_op_gemm_fold: epilogue %d has no folded-LayerNorm form", epi);
+  if (epi == EPI_BIAS_RESID_F32 ? (stats_in != nullptr) : (stats_out != nullptr || xb_out != nullptr))
+    return set_error("inksam_op_gemm_fold: epilogue %d given the other side's arguments", epi);
+  if (stats_in != nullptr && (!colsum || !bias || stats_np < 1)) return set_error("inksam_op_gemm_fold: stats_in needs colsum, bias and stats_np");
+  if ((stats_out != nullptr) != (xb_out != nullptr)) return set_error("inksam_op_gemm_fold: stats_out and xb_out come together");
+  if (epi == EPI_BIAS_RESID_F32 && stats_out != nullptr) epi = EPI_BIAS_RESID_STATS_F32;
+  if (epi == EPI_BIAS_BF16 && stats_in != nullptr) epi = EPI_FOLD_BF16;
+  if (epi == EPI_BIAS_GELU_BF16 && stats_in != nullptr) epi = EPI_FOLD_GELU_BF16;
+  GemmArgs g{};
+  g.M = M; g.N = N; g.K = K; g.ldo = ldo; g.out = out; g.bias = bias; g.resid = resid; g.win_remap = win_remap;
+  g.stats_out = stats_out; g.xb_out = xb_out; g.stats_in = stats_in; g.colsum = colsum; g.stats_np = stats_np; g.fold_eps = eps;
+  return launch_gemm(2, 0, 256, epi, A, lda, W, ldw, g, device_sms(), static_cast<cudaStream_t>(stream));
 }
 
 int inksam_op_patchify(const void* images, int dtype, int B, const int* hw, long long img_stride, long long row_pitch,

@@ -37,7 +37,9 @@ int launch_attention(int windowed, const void* qkv, const void* rel, void* out, 
 int launch_patchify(const void* images, int dtype, int B, const int* hw, long long img_stride, long long row_pitch,
                     long long plane_stride, const float* mean, const float* stdv, void* out, cudaStream_t st);
 int launch_layernorm_bf16(const float* x, const float* w, const float* b, void* out, int M, int D, float eps, int plain,
-                          cudaStream_t st);
+                          float* stats, cudaStream_t st);
+int launch_fold_ln_weights(const float* W, const float* gamma, const float* beta, const float* bias, void* w_out, float* colsum,
+                           float* bias_out, int N, int K, cudaStream_t st);
 int launch_fill_pad_rows(void* qkv, const float* bias, int B, int cols, cudaStream_t st);
 int launch_repack(const float* in, void* out, int out_bf16, const long long* ishape, int ndim, const int* perm,
                   cudaStream_t st);

@@ -78,11 +78,13 @@ int launch_patchify(const void* images, int dtype, int B, const int* hw, long lo
 // ------------------------------------------------------------------------------------------------ LayerNorm
 // nn.LayerNorm over the last dim, fp32 statistics, biased variance (SA/modeling/image_encoder.py:168,180,
 // eps 1e-6 from build_sam.py:72) -> bf16 activations for the next GEMM.  One warp per token, row held in registers.
-// plain != 0: no normalisation, just the bf16 cast (input of the neck's 1x1 conv).
+// plain != 0: no normalisation, just the bf16 cast; with `stats` also the row's (sum, sum of squares) -- the form the
+// first block's qkv GEMM reads when the LayerNorm is folded into it (gemm_args.h; later blocks get both from the
+// epilogue of the GEMM that wrote the residual stream).
 template <int MAXC>
 __global__ void __launch_bounds__(256) layernorm_bf16_kernel(const float* __restrict__ x, const float* __restrict__ w,
                                                              const float* __restrict__ bsh, __nv_bfloat16* __restrict__ out,
-                                                             int M, int D, float eps, int plain) {
+                                                             int M, int D, float eps, int plain, float2* __restrict__ stats) {
   pdl_launch_dependents();  // the consuming GEMM (launched with PDL) may run its prologue under this kernel's last wave
   const int row = blockIdx.x * 8 + (threadIdx.x >> 5);
   const int lane = threadIdx.x & 31;
@@ -100,6 +102,20 @@ __global__ void __launch_bounds__(256) layernorm_bf16_kernel(const float* __rest
     }
   }
   float mean = 0.f, rstd = 1.f;
+  if (plain && stats != nullptr) {
+    float sq = 0.f;
+#pragma unroll
+    for (int i = 0; i < MAXC; ++i) {
+      const int c = lane + 32 * i;
+      if (c < nch) sq += (v[i].x * v[i].x + v[i].y * v[i].y) + (v[i].z * v[i].z + v[i].w * v[i].w);
+    }
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) {
+      sum += __shfl_xor_sync(0xffffffffu, sum, o);
+      sq += __shfl_xor_sync(0xffffffffu, sq, o);
+    }
+    if (lane == 0) stats[row] = make_float2(sum, sq);
+  }
   if (!plain) {
 #pragma unroll
     for (int o = 16; o > 0; o >>= 1) sum += __shfl_xor_sync(0xffffffffu, sum, o);
@@ -141,13 +157,54 @@ __global__ void __launch_bounds__(256) layernorm_bf16_kernel(const float* __rest
 }
 
 int launch_layernorm_bf16(const float* x, const float* w, const float* b, void* out, int M, int D, float eps, int plain,
-                          cudaStream_t st) {
+                          float* stats, cudaStream_t st) {
+  if (stats != nullptr && !plain) return set_error("layernorm: row statistics are only written in the plain (cast) mode");
   if (D % 4 != 0 || D > 1280) return set_error("layernorm: D=%d must be a multiple of 4 and <= 1280", D);
   const unsigned grid = (unsigned)((M + 7) / 8);
   auto* o = static_cast<__nv_bfloat16*>(out);
-  if (D <= 256) layernorm_bf16_kernel<2><<<grid, 256, 0, st>>>(x, w, b, o, M, D, eps, plain);
-  else if (D <= 768) layernorm_bf16_kernel<6><<<grid, 256, 0, st>>>(x, w, b, o, M, D, eps, plain);
-  else layernorm_bf16_kernel<10><<<grid, 256, 0, st>>>(x, w, b, o, M, D, eps, plain);
+  if (D <= 256) layernorm_bf16_kernel<2><<<grid, 256, 0, st>>>(x, w, b, o, M, D, eps, plain, reinterpret_cast<float2*>(stats));
+  else if (D <= 768) layernorm_bf16_kernel<6><<<grid, 256, 0, st>>>(x, w, b, o, M, D, eps, plain, reinterpret_cast<float2*>(stats));
+  else layernorm_bf16_kernel<10><<<grid, 256, 0, st>>>(x, w, b, o, M, D, eps, plain, reinterpret_cast<float2*>(stats));
+  CUDA_TRY(cudaGetLastError());
+  return 0;
+}
+
+// ------------------------------------------------------------------------------------------------ LayerNorm fold
+// Weight side of folding `Linear(LayerNorm(x))` into one GEMM on the raw bf16 x (gemm_args.h):
+//   w_out[n][k] = bf16(gamma[k] * W[n][k]);  colsum[n] = sum_k w_out[n][k]  (of the ROUNDED values, so that the mean term
+//   cancels exactly what the tensor cores accumulate);  bias_out[n] = bias[n] + sum_k W[n][k] * beta[k].
+// One warp per output row; runs once per weight load.
+__global__ void __launch_bounds__(256) fold_ln_weights_kernel(const float* __restrict__ W, const float* __restrict__ gamma,
+                                                              const float* __restrict__ beta, const float* __restrict__ bias,
+                                                              __nv_bfloat16* __restrict__ w_out, float* __restrict__ colsum,
+                                                              float* __restrict__ bias_out, int N, int K) {
+  const int n = blockIdx.x * 8 + (threadIdx.x >> 5), lane = threadIdx.x & 31;
+  if (n >= N) return;
+  const float* wr = W + (size_t)n * K;
+  __nv_bfloat16* orow = w_out + (size_t)n * K;
+  float cs = 0.f, bb = 0.f;
+  for (int k = lane; k < K; k += 32) {
+    const float w = wr[k];
+    const __nv_bfloat16 r = __float2bfloat16_rn(w * gamma[k]);
+    orow[k] = r;
+    cs += __bfloat162float(r);
+    bb = fmaf(w, beta[k], bb);
+  }
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) {
+    cs += __shfl_xor_sync(0xffffffffu, cs, o);
+    bb += __shfl_xor_sync(0xffffffffu, bb, o);
+  }
+  if (lane == 0) {
+    colsum[n] = cs;
+    bias_out[n] = bias[n] + bb;
+  }
+}
+
+int launch_fold_ln_weights(const float* W, const float* gamma, const float* beta, const float* bias, void* w_out, float* colsum,
+                           float* bias_out, int N, int K, cudaStream_t st) {
+  fold_ln_weights_kernel<<<(unsigned)((N + 7) / 8), 256, 0, st>>>(W, gamma, beta, bias, static_cast<__nv_bfloat16*>(w_out), colsum,
+                                                                 bias_out, N, K);
   CUDA_TRY(cudaGetLastError());
   return 0;
 }

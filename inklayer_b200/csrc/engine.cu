@@ -22,7 +22,10 @@ struct Tensor {
 
 struct BlockW {
   const float *n1_w, *n1_b, *n2_w, *n2_b, *qkv_b, *proj_b, *lin1_b, *lin2_b;
-  const void *qkv_w, *proj_w, *lin1_w, *lin2_w;
+  const void *proj_w, *lin2_w;
+  // norm1 -> qkv and norm2 -> lin1 with the LayerNorm folded in (gemm_args.h): bf16 gamma o W, its row sums, b + W beta
+  void *qkv_w, *lin1_w;
+  float *qkv_cs, *qkv_bf, *lin1_cs, *lin1_bf;
   void* rel;  // bf16 rel-pos table [256][hd] (global) or [64][hd] (windowed)
   bool global;
 };
@@ -187,8 +190,8 @@ int inksam_load_tensor(inksam_handle* h, const char* key_c, const float* data, c
   const int* perm = nullptr;
   static const int perm_0231[4] = {0, 2, 3, 1}, perm_2310[4] = {2, 3, 1, 0};
   if (starts_with(key, "image_encoder.") && ends_with(key, ".weight") && ndim >= 2 &&
-      (ends_with(key, "attn.qkv.weight") || ends_with(key, "attn.proj.weight") || ends_with(key, "mlp.lin1.weight") ||
-       ends_with(key, "mlp.lin2.weight") || key == "image_encoder.patch_embed.proj.weight" ||
+      // (qkv and lin1 of the blocks stay fp32: finalize folds the preceding LayerNorm's gamma in before rounding)
+      (ends_with(key, "attn.proj.weight") || ends_with(key, "mlp.lin2.weight") || key == "image_encoder.patch_embed.proj.weight" ||
        key == "image_encoder.neck.0.weight" || key == "image_encoder.neck.2.weight"))
     to_bf16 = true;
   if (key == "image_encoder.neck.2.weight") perm = perm_0231;  // [o][c][ky][kx] -> [o][ky][kx][c]
@@ -344,12 +347,26 @@ extern "C" int inksam_finalize_weights(inksam_handle* h, void* stream) {
     INK_TRY(need_f32(h, p + "norm1.bias", &b.n1_b));
     INK_TRY(need_f32(h, p + "norm2.weight", &b.n2_w));
     INK_TRY(need_f32(h, p + "norm2.bias", &b.n2_b));
-    INK_TRY(need_any(h, p + "attn.qkv.weight", &b.qkv_w));
     INK_TRY(need_f32(h, p + "attn.qkv.bias", &b.qkv_b));
     INK_TRY(need_any(h, p + "attn.proj.weight", &b.proj_w));
     INK_TRY(need_f32(h, p + "attn.proj.bias", &b.proj_b));
-    INK_TRY(need_any(h, p + "mlp.lin1.weight", &b.lin1_w));
     INK_TRY(need_f32(h, p + "mlp.lin1.bias", &b.lin1_b));
+    {
+      const float *wq, *w1;
+      INK_TRY(need_f32(h, p + "attn.qkv.weight", &wq));
+      INK_TRY(need_f32(h, p + "mlp.lin1.weight", &w1));
+      const Tensor* t1 = find(h, p + "mlp.lin1.weight");
+      if (t1->shape.size() != 2 || t1->shape[0] != 4 * D || t1->shape[1] != D)
+        return set_error("finalize: %smlp.lin1.weight is not [%d,%d] (mlp_ratio 4)", p.c_str(), 4 * D, D);
+      INK_TRY(dev_alloc(h, &b.qkv_w, (size_t)3 * D * D * 2));
+      INK_TRY(dev_alloc(h, &b.lin1_w, (size_t)4 * D * D * 2));
+      void* v;
+      INK_TRY(dev_alloc(h, &v, (size_t)14 * D * 4));
+      b.qkv_cs = static_cast<float*>(v); b.qkv_bf = b.qkv_cs + 3 * D; b.lin1_cs = b.qkv_bf + 3 * D; b.lin1_bf = b.lin1_cs + 4 * D;
+      h->launches += 2;
+      INK_TRY(launch_fold_ln_weights(wq, b.n1_w, b.n1_b, b.qkv_b, b.qkv_w, b.qkv_cs, b.qkv_bf, 3 * D, D, st));
+      INK_TRY(launch_fold_ln_weights(w1, b.n2_w, b.n2_b, b.lin1_b, b.lin1_w, b.lin1_cs, b.lin1_bf, 4 * D, D, st));
+    }
     INK_TRY(need_any(h, p + "mlp.lin2.weight", &b.lin2_w));
     INK_TRY(need_f32(h, p + "mlp.lin2.bias", &b.lin2_b));
     INK_TRY(build_rel_table(h, p + "attn.", b.global, &b.rel, st));
@@ -389,7 +406,9 @@ int encode_chunk(inksam_handle* h, const void* images, int dtype, int B, const i
   const size_t sz_pad = align_up((size_t)B * 66 * 66 * 256 * 2);
   const size_t sz_patch = align_up((size_t)M * 768 * 2);
   const size_t sz_hp = sz_h > sz_patch ? sz_h : sz_patch;  // patches alias the MLP hidden buffer
-  INK_TRY(grow(&h->enc_ws, &h->enc_ws_bytes, sz_x + sz_xn + sz_qkv + sz_attn + sz_hp + sz_pad));
+  const int np = gemm_stats_partials(D);  // partial row statistics written by the proj / lin2 epilogues
+  const size_t sz_stats = align_up((size_t)M * np * 2 * 4);
+  INK_TRY(grow(&h->enc_ws, &h->enc_ws_bytes, sz_x + sz_xn + sz_qkv + sz_attn + sz_hp + sz_pad + sz_stats));
   char* base = static_cast<char*>(h->enc_ws);
   float* x = reinterpret_cast<float*>(base);
   void* xn = base + sz_x;
@@ -397,6 +416,7 @@ int encode_chunk(inksam_handle* h, const void* images, int dtype, int B, const i
   void* attn = base + sz_x + sz_xn + sz_qkv;
   void* hbuf = base + sz_x + sz_xn + sz_qkv + sz_attn;
   void* pad = base + sz_x + sz_xn + sz_qkv + sz_attn + sz_hp;
+  float* stats = reinterpret_cast<float*>(base + sz_x + sz_xn + sz_qkv + sz_attn + sz_hp + sz_pad);
 
   const float *pos, *patch_b, *n1w, *n1b, *n3w, *n3b;
   const void *patch_w, *neck0, *neck2;
@@ -418,12 +438,17 @@ int encode_chunk(inksam_handle* h, const void* images, int dtype, int B, const i
     c.g.M = M; c.g.N = D; c.g.K = 768; c.g.ldo = D; c.g.out = x; c.g.bias = patch_b; c.g.rowadd = pos; c.g.rowadd_mod = 4096;
     INK_TRY(run_gemm(h, c, st));
   }
+  // Blocks (image_encoder.py:180-197).  The two LayerNorms are folded into the GEMMs around them (gemm_args.h): whoever
+  // writes the residual stream x (fp32) also writes xn = bf16(x) and per-row partial sums; qkv and lin1 run on xn with
+  // gamma folded into their weights and apply mean / rstd in the epilogue.  Only the first block needs a separate pass.
+  ++h->launches;
+  INK_TRY(launch_layernorm_bf16(x, nullptr, nullptr, xn, M, D, 0.f, 1, stats, st));
+  int np_in = 1;
   for (const BlockW& b : h->blocks) {
-    ++h->launches;
-    INK_TRY(launch_layernorm_bf16(x, b.n1_w, b.n1_b, xn, M, D, 1e-6f, 0, st));
     {
-      G c; c.epi = EPI_BIAS_BF16; c.A = xn; c.lda = D; c.W = b.qkv_w; c.ldw = D;
-      c.g.M = M; c.g.N = 3 * D; c.g.K = D; c.g.ldo = 3 * D; c.g.out = qkv; c.g.bias = b.qkv_b; c.g.win_remap = b.global ? 0 : 1;
+      G c; c.epi = EPI_FOLD_BF16; c.A = xn; c.lda = D; c.W = b.qkv_w; c.ldw = D;
+      c.g.M = M; c.g.N = 3 * D; c.g.K = D; c.g.ldo = 3 * D; c.g.out = qkv; c.g.bias = b.qkv_bf; c.g.win_remap = b.global ? 0 : 1;
+      c.g.stats_in = stats; c.g.colsum = b.qkv_cs; c.g.stats_np = np_in; c.g.fold_eps = 1e-6f;
       INK_TRY(run_gemm(h, c, st));
     }
     if (!b.global) {
@@ -437,26 +462,28 @@ int encode_chunk(inksam_handle* h, const void* images, int dtype, int B, const i
       INK_TRY(launch_attention(b.global ? 0 : 1, qkv, b.rel, attn, B, heads, hd, st));
     }
     {
-      G c; c.epi = EPI_BIAS_RESID_F32; c.A = attn; c.lda = D; c.W = b.proj_w; c.ldw = D;
+      G c; c.epi = EPI_BIAS_RESID_STATS_F32; c.A = attn; c.lda = D; c.W = b.proj_w; c.ldw = D;
       c.g.M = M; c.g.N = D; c.g.K = D; c.g.ldo = D; c.g.out = x; c.g.bias = b.proj_b; c.g.resid = x;
+      c.g.stats_out = stats; c.g.xb_out = xn;
       INK_TRY(run_gemm(h, c, st));
     }
-    ++h->launches;
-    INK_TRY(launch_layernorm_bf16(x, b.n2_w, b.n2_b, xn, M, D, 1e-6f, 0, st));
+    np_in = np;
     {
-      G c; c.epi = EPI_BIAS_GELU_BF16; c.A = xn; c.lda = D; c.W = b.lin1_w; c.ldw = D;
-      c.g.M = M; c.g.N = 4 * D; c.g.K = D; c.g.ldo = 4 * D; c.g.out = hbuf; c.g.bias = b.lin1_b;
+      G c; c.epi = EPI_FOLD_GELU_BF16; c.A = xn; c.lda = D; c.W = b.lin1_w; c.ldw = D;
+      c.g.M = M; c.g.N = 4 * D; c.g.K = D; c.g.ldo = 4 * D; c.g.out = hbuf; c.g.bias = b.lin1_bf;
+      c.g.stats_in = stats; c.g.colsum = b.lin1_cs; c.g.stats_np = np_in; c.g.fold_eps = 1e-6f;
       INK_TRY(run_gemm(h, c, st));
     }
     {
-      G c; c.epi = EPI_BIAS_RESID_F32; c.A = hbuf; c.lda = 4 * D; c.W = b.lin2_w; c.ldw = 4 * D;
+      G c; c.epi = EPI_BIAS_RESID_STATS_F32; c.A = hbuf; c.lda = 4 * D; c.W = b.lin2_w; c.ldw = 4 * D;
       c.g.M = M; c.g.N = D; c.g.K = 4 * D; c.g.ldo = D; c.g.out = x; c.g.bias = b.lin2_b; c.g.resid = x;
+      c.g.stats_out = stats; c.g.xb_out = xn;
       INK_TRY(run_gemm(h, c, st));
     }
   }
   // neck: 1x1 conv + LayerNorm2d -> zero-bordered bf16 map; 3x3 conv (implicit GEMM over 9 taps) + LayerNorm2d -> NCHW fp32
-  ++h->launches;
-  INK_TRY(launch_layernorm_bf16(x, nullptr, nullptr, xn, M, D, 0.f, 1, st));
+  // (the neck's A operand bf16(x) was written by the last block's lin2 epilogue)
+  if (h->blocks.empty()) return set_error("encode: no encoder blocks");
   CUDA_TRY(cudaMemsetAsync(pad, 0, (size_t)B * 66 * 66 * 256 * 2, st));
   {
     G c; c.epi = EPI_LN_BF16_PAD; c.A = xn; c.lda = D; c.W = neck0; c.ldw = D;

@@ -15,6 +15,11 @@ enum GemmEpi : int {
   EPI_BIAS_F32 = 7,        // out_f32 = acc + bias
   EPI_UPSCALE1 = 8,        // decoder ConvT(256->64,k2,s2)+LayerNorm2d+GELU, out [K][128][128][64] fp32
   EPI_UPSCALE2_MASK = 9,   // decoder ConvT(64->32,k2,s2)+GELU, dot with hyper_in -> low-res logits
+  // LayerNorm folded into the GEMMs either side of it (see stats_* below); separate kernels, so that the plain
+  // epilogues above carry none of this
+  EPI_FOLD_BF16 = 10,      // out_bf16 = rstd * acc - rstd * mean * colsum + bias          (A = raw bf16 x)
+  EPI_FOLD_GELU_BF16 = 11, // out_bf16 = gelu_erf(the same)
+  EPI_BIAS_RESID_STATS_F32 = 12,  // EPI_BIAS_RESID_F32 + per-row partial (sum, sum of squares) + bf16 copy of the output
 };
 
 struct GemmArgs {
@@ -34,6 +39,20 @@ struct GemmArgs {
   int win_remap;       // EPI_BIAS_BF16: store token rows in 14x14-window order (windowed encoder blocks)
   int resid_mod;       // EPI_RESID_LN_F32: resid row = m % resid_mod when non-zero (keys shared by all boxes)
   const int* row_img;  // EPI_RESID_LN_F32 with resid_mod: resid row += row_img[m / resid_mod] * resid_mod (keys of the box's image)
+  // LayerNorm folded into the GEMMs either side of it (encoder blocks).  The producer of the residual
+  // stream also emits what the LayerNorm would have read; the consumer applies the normalisation to its accumulator:
+  //   LN(x) W^T + b  ==  rstd * (x (gamma o W)^T) - rstd * mean * colsum(gamma o W) + (b + W beta)
+  float* stats_out;       // EPI_BIAS_RESID_STATS_F32: [M][stats_np][2] partial (sum, sum of squares) of each output row, one per
+                          // (n tile, column half) = gemm_stats_partials(N) of them
+  void* xb_out;           // EPI_BIAS_RESID_STATS_F32: bf16 copy of the output rows [M][ldo] (A of the next GEMM)
+  const float* stats_in;  // EPI_FOLD_*: partials of the rows of A over its K columns
+  const float* colsum;    // [N] sum over k of the bf16 weight row (with stats_in; `bias` then holds b + W beta)
+  int stats_np;           // partials per row in stats_in
+  float fold_eps;         // eps of the folded LayerNorm
 };
+
+// Partials per row that an EPI_BIAS_RESID_STATS_F32 launch with N output columns writes to stats_out (BN = 256, two column
+// halves per tile).
+inline int gemm_stats_partials(int N) { return 2 * ((N + 255) / 256); }
 
 }  // namespace inksam

@@ -140,6 +140,10 @@ int launch_gemm(int cg, int tf32, int bn, int epi, const void* A, int lda, const
   const int esz = tf32 ? 4 : 2;
   if (g.N % 32 != 0) return set_error("gemm: N=%d must be a multiple of 32", g.N);
   if ((g.K * esz) % 16 != 0) return set_error("gemm: K=%d row bytes must be a multiple of 16", g.K);
+  if (epi_is_fold(epi) && (!g.stats_in || !g.colsum || !g.bias || g.stats_np < 1))
+    return set_error("gemm: the folded-LayerNorm epilogue needs stats_in, colsum, bias and stats_np >= 1");
+  if (epi == EPI_BIAS_RESID_STATS_F32 && (!g.stats_out || !g.xb_out))
+    return set_error("gemm: the residual + statistics epilogue needs stats_out and xb_out");
   CUtensorMap tA, tB;
   if (g.a_conv3x3) {
     if (make_tmap_conv3(&tA, A, g.M / 4096, g.conv_c)) return -1;
@@ -160,6 +164,9 @@ int launch_gemm(int cg, int tf32, int bn, int epi, const void* A, int lda, const
   GEMM_CASE(2, 0, 256, EPI_BIAS_GELU_BF16)
   GEMM_CASE(1, 0, 256, EPI_BIAS_RESID_F32)
   GEMM_CASE(2, 0, 256, EPI_BIAS_RESID_F32)
+  GEMM_CASE(2, 0, 256, EPI_FOLD_BF16)
+  GEMM_CASE(2, 0, 256, EPI_FOLD_GELU_BF16)
+  GEMM_CASE(2, 0, 256, EPI_BIAS_RESID_STATS_F32)
   GEMM_CASE(1, 0, 256, EPI_BIAS_ROWADD_F32)
   GEMM_CASE(2, 0, 256, EPI_BIAS_ROWADD_F32)
   GEMM_CASE(1, 0, 256, EPI_LN_BF16_PAD)

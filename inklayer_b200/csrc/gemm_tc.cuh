@@ -93,7 +93,9 @@ struct GemmCfg {
   static constexpr int TMEM_COLS = 2 * BN;       // double-buffered accumulators (power of two: 256 or 512)
 };
 
-__host__ __device__ constexpr int gemm_staged(int epi) { return epi == EPI_BIAS_RESID_F32 ? 1 : 0; }
+__host__ __device__ constexpr bool epi_is_resid(int epi) { return epi == EPI_BIAS_RESID_F32 || epi == EPI_BIAS_RESID_STATS_F32; }
+__host__ __device__ constexpr bool epi_is_fold(int epi) { return epi == EPI_FOLD_BF16 || epi == EPI_FOLD_GELU_BF16; }
+__host__ __device__ constexpr int gemm_staged(int epi) { return epi_is_resid(epi) ? 1 : 0; }
 
 template <int CG, int TF32, int BN, int EPI>
 __global__ void __launch_bounds__(384, 1)
@@ -258,8 +260,8 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
       constexpr int NCH = BN / 32;
       constexpr int NCW = NCH / CSPLIT;  // 32-column chunks handled by this warp
       const int c_first = half * NCW;
-      constexpr bool kHasAdd = (EPI == EPI_BIAS_RESID_F32 || EPI == EPI_BIAS_ROWADD_F32);
-      constexpr bool kSimple = (EPI == EPI_BIAS_BF16 || EPI == EPI_BIAS_GELU_BF16 || EPI == EPI_BIAS_RESID_F32 ||
+      constexpr bool kHasAdd = (epi_is_resid(EPI) || EPI == EPI_BIAS_ROWADD_F32);
+      constexpr bool kSimple = (EPI == EPI_BIAS_BF16 || EPI == EPI_BIAS_GELU_BF16 || epi_is_fold(EPI) || epi_is_resid(EPI) ||
                                 EPI == EPI_BIAS_ROWADD_F32 || EPI == EPI_BIAS_F32);
       // residual / row-add operand of this thread's row, fetched one chunk ahead of its use (the first chunk even
       // before the accumulator is complete).  In-place use (out == resid) is safe: a chunk is loaded before the
@@ -268,12 +270,12 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
       const float* add_row = nullptr;
       if constexpr (kHasAdd) {
         const int mm = row_ok ? m : 0;
-        if constexpr (EPI == EPI_BIAS_RESID_F32) add_row = g.resid + (size_t)mm * g.ldo + n0;
+        if constexpr (epi_is_resid(EPI)) add_row = g.resid + (size_t)mm * g.ldo + n0;
         else add_row = g.rowadd + (size_t)(mm % g.rowadd_mod) * g.N + n0;
         if (n0 + c_first * 32 < g.N) {
 #pragma unroll
           for (int h = 0; h < 4; ++h) {
-            if constexpr (EPI == EPI_BIAS_RESID_F32)
+            if constexpr (epi_is_resid(EPI))
               ld_global_v8_stream(add_row + c_first * 32 + h * 8, *reinterpret_cast<uint32_t(*)[8]>(&radd[0][h * 8]));
             else
               ld_global_v8(add_row + c_first * 32 + h * 8, *reinterpret_cast<uint32_t(*)[8]>(&radd[0][h * 8]));
@@ -283,7 +285,7 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
       mbar_wait(tfull_bar(as), aphase);
       tc_fence_after();
 
-      if constexpr (EPI == EPI_BIAS_RESID_F32) {
+      if constexpr (epi_is_resid(EPI)) {
         // out = resid + acc + bias, fp32.  Thread-per-row global stores of a 32 x 32 fp32 sub-tile touch 32 lines per
         // instruction; instead each warp writes 32 x 16 halves into 64B-swizzled staging buffers (conflict-free 16-byte
         // stores) and one lane sends them out with TMA stores.  Two buffers per warp: a buffer is rewritten once the
@@ -293,6 +295,10 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
         const uint32_t sbuf = staging_base + (uint32_t)(warp - 4) * 4096u;
         const int row0 = m - lane;
         const uint32_t srow = (uint32_t)lane * 64u, sx = (uint32_t)((lane >> 1) & 3);
+        // folded LayerNorm (gemm_args.h): this thread's share of its row's sum and sum of squares, and a bf16 copy
+        uint64_t rs2 = f2_pack(0.f, 0.f), rq2 = rs2;
+        constexpr bool emit = (EPI == EPI_BIAS_RESID_STATS_F32);
+        __nv_bfloat16* xb_row = reinterpret_cast<__nv_bfloat16*>(g.xb_out) + (size_t)(row_ok ? m : 0) * g.ldo;
 #pragma unroll
         for (int ci = 0; ci < NCW; ++ci) {
           const int c = c_first + ci;
@@ -310,6 +316,7 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
               if (lane == 0) bulk_wait_group_read<1>();
               __syncwarp();
               const uint32_t sb = sbuf + (uint32_t)hf * 2048u;
+              uint32_t pk[8];
 #pragma unroll
               for (int j = 0; j < 4; ++j) {
                 const int e = hf * 16 + 4 * j;          // column of the chunk
@@ -323,6 +330,16 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
                 f2_unpack(f2_add(f2_add(f2_pack(f[e + 2], f[e + 3]), f2_pack(b4.z, b4.w)),
                                  f2_pack(__uint_as_float(radd[ci & 1][e + 2]), __uint_as_float(radd[ci & 1][e + 3]))), x2, x3);
                 st_shared_v4(sb + srow + (((uint32_t)j ^ sx) << 4), x0, x1, x2, x3);
+                if constexpr (emit) {
+                  const uint64_t a2 = f2_pack(x0, x1), b2 = f2_pack(x2, x3);
+                  rs2 = f2_add(rs2, f2_add(a2, b2));
+                  rq2 = f2_fma(a2, a2, f2_fma(b2, b2, rq2));
+                  pk[2 * j] = pack_bf16x2(x0, x1);
+                  pk[2 * j + 1] = pack_bf16x2(x2, x3);
+                }
+              }
+              if constexpr (emit) {
+                if (row_ok) st_global_v8(xb_row + col + hf * 16, pk);
               }
               fence_proxy_async_smem();
               __syncwarp();
@@ -333,9 +350,32 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
             }
           }
         }
+        if (emit && row_ok) {
+          float s0, s1, q0, q1;
+          f2_unpack(rs2, s0, s1);
+          f2_unpack(rq2, q0, q1);
+          const int np = CSPLIT * tiles_n;
+          reinterpret_cast<float2*>(g.stats_out)[(size_t)m * np + n_blk * CSPLIT + half] = make_float2(s0 + s1, q0 + q1);
+        }
       } else if constexpr (kSimple) {
         uint32_t v[32];
         float* f = reinterpret_cast<float*>(v);
+        // folded LayerNorm (gemm_args.h): out = rstd * acc + (-rstd * mean) * colsum + bias
+                constexpr bool fold = epi_is_fold(EPI);
+        uint64_t rstd2 = 0, nrm2 = 0;
+        if constexpr (fold) {
+          const float2* sp = reinterpret_cast<const float2*>(g.stats_in) + (size_t)(row_ok ? m : 0) * g.stats_np;
+          float s = 0.f, ss = 0.f;
+          for (int i = 0; i < g.stats_np; ++i) {
+            const float2 t = sp[i];
+            s += t.x; ss += t.y;
+          }
+          const float inv_k = 1.0f / (float)g.K;
+          const float mean = s * inv_k;
+          const float rstd = rsqrtf(fmaxf(ss * inv_k - mean * mean, 0.f) + g.fold_eps);
+          rstd2 = f2_pack(rstd, rstd);
+          nrm2 = f2_pack(-rstd * mean, -rstd * mean);
+        }
 #pragma unroll
         for (int ci = 0; ci < NCW; ++ci) {
           const int c = c_first + ci;
@@ -350,7 +390,16 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
               }
             }
             tmem_ld_wait();
-            if (g.bias != nullptr) {
+            if constexpr (fold) {
+#pragma unroll
+              for (int j = 0; j < 32; j += 4) {
+                const float4 b4 = __ldg(reinterpret_cast<const float4*>(g.bias + col + j));
+                const float4 c4 = __ldg(reinterpret_cast<const float4*>(g.colsum + col + j));
+                f2_unpack(f2_fma(rstd2, f2_pack(f[j], f[j + 1]), f2_fma(nrm2, f2_pack(c4.x, c4.y), f2_pack(b4.x, b4.y))), f[j], f[j + 1]);
+                f2_unpack(f2_fma(rstd2, f2_pack(f[j + 2], f[j + 3]), f2_fma(nrm2, f2_pack(c4.z, c4.w), f2_pack(b4.z, b4.w))), f[j + 2],
+                          f[j + 3]);
+              }
+            } else if (g.bias != nullptr) {
 #pragma unroll
               for (int j = 0; j < 32; j += 4) {
                 const float4 b4 = __ldg(reinterpret_cast<const float4*>(g.bias + col + j));
@@ -358,11 +407,11 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
                 f2_unpack(f2_add(f2_pack(f[j + 2], f[j + 3]), f2_pack(b4.z, b4.w)), f[j + 2], f[j + 3]);
               }
             }
-            if constexpr (EPI == EPI_BIAS_GELU_BF16) {
+            if constexpr (EPI == EPI_BIAS_GELU_BF16 || EPI == EPI_FOLD_GELU_BF16) {
 #pragma unroll
               for (int j = 0; j < 32; j += 2) gelu_erf2(f[j], f[j + 1]);
             }
-            if constexpr (EPI == EPI_BIAS_BF16 || EPI == EPI_BIAS_GELU_BF16) {
+            if constexpr (EPI == EPI_BIAS_BF16 || EPI == EPI_BIAS_GELU_BF16 || fold) {
               if (row_ok) {
                 __nv_bfloat16* o = reinterpret_cast<__nv_bfloat16*>(g.out) + (size_t)mo * g.ldo + col;
 #pragma unroll
@@ -631,7 +680,7 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
   }
 
   // ---------------------------------------------------------------- teardown
-  if constexpr (EPI == EPI_BIAS_RESID_F32) {
+  if constexpr (epi_is_resid(EPI)) {
     if (warp >= 4 && lane == 0) bulk_wait_group_all();  // this warp's TMA stores have left shared memory and are complete
   }
   tc_fence_before();
