@@ -57,9 +57,9 @@ int inksam_op_layernorm(const float* x, const float* w, const float* b, void* ou
  *                              bias_out [N] = bias + W beta.
  *   inksam_op_row_stats_bf16:  x fp32 [M][D] -> out bf16 [M][D] (plain cast) and stats [M][2] = (sum, sum of squares).
  *   inksam_op_gemm_fold:       CTA-pair bf16 GEMM, BN 256.  epi 2 (bias + fp32 residual): also writes stats_out
- *                              [M][inksam_op_gemm_stats_partials(N)][2] and the bf16 copy xb_out [M][ldo] of its output
+ *                              [inksam_op_gemm_stats_partials(N)][M][2] and the bf16 copy xb_out [M][ldo] of its output
  *                              (both, or both null for the plain epilogue).  epi 0 / 1 (bf16 out, optional GELU): A is the raw bf16 x, W / colsum /
- *                              bias come from inksam_op_fold_ln_weights, stats_in [M][stats_np][2] are partials of the
+ *                              bias come from inksam_op_fold_ln_weights, stats_in [stats_np][M][2] are partials of the
  *                              rows of A over its K columns. */
 int inksam_op_fold_ln_weights(const float* W, const float* gamma, const float* beta, const float* bias, void* w_out,
                               float* colsum, float* bias_out, int N, int K, void* stream);

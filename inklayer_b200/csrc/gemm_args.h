@@ -42,7 +42,7 @@ struct GemmArgs {
   // LayerNorm folded into the GEMMs either side of it (encoder blocks).  The producer of the residual
   // stream also emits what the LayerNorm would have read; the consumer applies the normalisation to its accumulator:
   //   LN(x) W^T + b  ==  rstd * (x (gamma o W)^T) - rstd * mean * colsum(gamma o W) + (b + W beta)
-  float* stats_out;       // EPI_BIAS_RESID_STATS_F32: [M][stats_np][2] partial (sum, sum of squares) of each output row, one per
+  float* stats_out;       // EPI_BIAS_RESID_STATS_F32: [stats_np][M][2] partial (sum, sum of squares) of each output row, one per
                           // (n tile, column half) = gemm_stats_partials(N) of them
   void* xb_out;           // EPI_BIAS_RESID_STATS_F32: bf16 copy of the output rows [M][ldo] (A of the next GEMM)
   const float* stats_in;  // EPI_FOLD_*: partials of the rows of A over its K columns

@@ -54,6 +54,22 @@ int make_tmap_f32_out(CUtensorMap* out, const void* base, uint64_t rows, uint64_
   return 0;
 }
 
+// bf16 row-major [rows][cols] copy of the fp32 output (EPI_BIAS_RESID_STATS_F32): box = 32 columns (64 bytes) x 32 rows,
+// 64B swizzle -- the staging geometry of an fp32 half.
+int make_tmap_bf16_out(CUtensorMap* out, const void* base, uint64_t rows, uint64_t cols, uint64_t ld_elems) {
+  if (fetch_encode()) return set_error("cuTensorMapEncodeTiled entry point not available");
+  cuuint64_t dims[2] = {cols, rows};
+  cuuint64_t strides[1] = {ld_elems * 2};
+  cuuint32_t box[2] = {32, 32};
+  cuuint32_t estr[2] = {1, 1};
+  CUresult r = g_encode(out, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2, const_cast<void*>(base), dims, strides, box, estr,
+                        CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_64B, CU_TENSOR_MAP_L2_PROMOTION_NONE,
+                        CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+  if (r != CUDA_SUCCESS) return set_error("cuTensorMapEncodeTiled(bf16 out) failed: %d (rows=%llu cols=%llu ld=%llu)", (int)r,
+                                          (unsigned long long)rows, (unsigned long long)cols, (unsigned long long)ld_elems);
+  return 0;
+}
+
 // bf16 row-major [rows][cols] matrix, arbitrary box; swizzle 128B (box_cols == 64) or 32B (box_cols == 16).
 int make_tmap_bf16_box(CUtensorMap* out, const void* base, uint64_t rows, uint64_t cols, uint64_t ld_elems,
                        uint32_t box_cols, uint32_t box_rows) {
@@ -87,7 +103,7 @@ int make_tmap_conv3(CUtensorMap* out, const void* base, int nb, int C) {
 }
 
 template <int CG, int TF32, int BN, int EPI>
-static int launch_one(const CUtensorMap& tA, const CUtensorMap& tB, const CUtensorMap& tO, const GemmArgs& g, int num_sms,
+static int launch_one(const CUtensorMap& tA, const CUtensorMap& tB, const CUtensorMap& tO, const CUtensorMap& tX, const GemmArgs& g, int num_sms,
                       cudaStream_t st) {
   using C = GemmCfg<CG, TF32, BN, gemm_staged(EPI)>;
   auto kern = gemm_tc_kernel<CG, TF32, BN, EPI>;
@@ -126,13 +142,13 @@ static int launch_one(const CUtensorMap& tA, const CUtensorMap& tB, const CUtens
   int clusters = max_clusters;
   if (tiles < clusters) clusters = tiles;
   cfg.gridDim = dim3(clusters * CG);
-  CUDA_TRY(cudaLaunchKernelEx(&cfg, kern, tA, tB, tO, g));
+  CUDA_TRY(cudaLaunchKernelEx(&cfg, kern, tA, tB, tO, tX, g));
   return 0;
 }
 
 #define GEMM_CASE(CG_, TF_, BN_, EPI_)                                             \
   if (cg == CG_ && tf32 == TF_ && bn == BN_ && epi == EPI_)                        \
-    return launch_one<CG_, TF_, BN_, EPI_>(tA, tB, tO, g, num_sms, st);
+    return launch_one<CG_, TF_, BN_, EPI_>(tA, tB, tO, tX, g, num_sms, st);
 
 // A: [M][K] (ld = lda elements) or the padded conv map when g.a_conv3x3; W: [N][K] row-major.
 int launch_gemm(int cg, int tf32, int bn, int epi, const void* A, int lda, const void* W, int ldw, GemmArgs g,
@@ -156,6 +172,12 @@ int launch_gemm(int cg, int tf32, int bn, int epi, const void* A, int lda, const
     if ((reinterpret_cast<uintptr_t>(g.out) & 15) != 0 || (g.ldo * 4) % 16 != 0)
       return set_error("gemm: the residual epilogue needs a 16-byte aligned output (ldo=%d)", g.ldo);
     if (make_tmap_f32_out(&tO, g.out, g.M, g.N, g.ldo)) return -1;
+  }
+  CUtensorMap tX = tA;  // bf16 copy of the residual output
+  if (epi == EPI_BIAS_RESID_STATS_F32) {
+    if ((reinterpret_cast<uintptr_t>(g.xb_out) & 15) != 0 || (g.ldo * 2) % 16 != 0)
+      return set_error("gemm: the bf16 copy needs a 16-byte aligned xb_out (ldo=%d)", g.ldo);
+    if (make_tmap_bf16_out(&tX, g.xb_out, g.M, g.N, g.ldo)) return -1;
   }
 
   GEMM_CASE(1, 0, 256, EPI_BIAS_BF16)

@@ -100,7 +100,7 @@ __host__ __device__ constexpr int gemm_staged(int epi) { return epi_is_resid(epi
 template <int CG, int TF32, int BN, int EPI>
 __global__ void __launch_bounds__(384, 1)
 gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB,
-               const __grid_constant__ CUtensorMap tmO, const GemmArgs g) {
+               const __grid_constant__ CUtensorMap tmO, const __grid_constant__ CUtensorMap tmX, const GemmArgs g) {
   using C = GemmCfg<CG, TF32, BN, gemm_staged(EPI)>;
   extern __shared__ uint8_t smem_raw[];
   const uint32_t smem_base = (smem_u32(smem_raw) + 1023u) & ~1023u;
@@ -244,6 +244,7 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
     const int half = (warp - 4) >> 2;                // which share of the columns is this warp's
     int as = 0;
     uint32_t aphase = 0;
+    uint32_t sk = 0;  // EPI_BIAS_RESID_STATS_F32: running count of this warp's TMA stores (staging buffer = sk & 1)
     for (int tile = cluster_id; tile < num_tiles; tile += num_clusters) {
       const int m_blk = tile / tiles_n, n_blk = tile % tiles_n;
       const int m = m_blk * C::BM * CG + (int)rank * C::BM + q * 32 + lane;
@@ -282,6 +283,22 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
           }
         }
       }
+      // folded LayerNorm (gemm_args.h): mean and rstd of this thread's row from the partial sums the producer of A left
+      // in stats_in ([np][M][2]: lanes read consecutive rows), added in fixed order; fetched before the accumulator wait
+      uint64_t rstd2 = 0, nrm2 = 0;
+      if constexpr (epi_is_fold(EPI)) {
+        const float2* sp = reinterpret_cast<const float2*>(g.stats_in) + (row_ok ? m : 0);
+        float s = 0.f, ss = 0.f;
+        for (int i = 0; i < g.stats_np; ++i) {
+          const float2 t = sp[(size_t)i * g.M];
+          s += t.x; ss += t.y;
+        }
+        const float inv_k = 1.0f / (float)g.K;
+        const float mean = s * inv_k;
+        const float rstd = rsqrtf(fmaxf(ss * inv_k - mean * mean, 0.f) + g.fold_eps);
+        rstd2 = f2_pack(rstd, rstd);
+        nrm2 = f2_pack(-rstd * mean, -rstd * mean);
+      }
       mbar_wait(tfull_bar(as), aphase);
       tc_fence_after();
 
@@ -298,7 +315,6 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
         // folded LayerNorm (gemm_args.h): this thread's share of its row's sum and sum of squares, and a bf16 copy
         uint64_t rs2 = f2_pack(0.f, 0.f), rq2 = rs2;
         constexpr bool emit = (EPI == EPI_BIAS_RESID_STATS_F32);
-        __nv_bfloat16* xb_row = reinterpret_cast<__nv_bfloat16*>(g.xb_out) + (size_t)(row_ok ? m : 0) * g.ldo;
 #pragma unroll
         for (int ci = 0; ci < NCW; ++ci) {
           const int c = c_first + ci;
@@ -311,12 +327,13 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
                 ld_global_v8_stream(add_row + (c + 1) * 32 + h * 8, *reinterpret_cast<uint32_t(*)[8]>(&radd[(ci + 1) & 1][h * 8]));
             }
             tmem_ld_wait();
+            uint32_t pk[emit ? 16 : 1];  // bf16 copy of this thread's 32 columns of the chunk
 #pragma unroll
             for (int hf = 0; hf < 2; ++hf) {
               if (lane == 0) bulk_wait_group_read<1>();
               __syncwarp();
-              const uint32_t sb = sbuf + (uint32_t)hf * 2048u;
-              uint32_t pk[8];
+              uint32_t sb = sbuf + (uint32_t)hf * 2048u;
+              if constexpr (emit) sb = sbuf + (sk++ & 1u) * 2048u;  // three stores per chunk: rotate instead
 #pragma unroll
               for (int j = 0; j < 4; ++j) {
                 const int e = hf * 16 + 4 * j;          // column of the chunk
@@ -334,17 +351,31 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
                   const uint64_t a2 = f2_pack(x0, x1), b2 = f2_pack(x2, x3);
                   rs2 = f2_add(rs2, f2_add(a2, b2));
                   rq2 = f2_fma(a2, a2, f2_fma(b2, b2, rq2));
-                  pk[2 * j] = pack_bf16x2(x0, x1);
-                  pk[2 * j + 1] = pack_bf16x2(x2, x3);
+                  pk[hf * 8 + 2 * j] = pack_bf16x2(x0, x1);
+                  pk[hf * 8 + 2 * j + 1] = pack_bf16x2(x2, x3);
                 }
-              }
-              if constexpr (emit) {
-                if (row_ok) st_global_v8(xb_row + col + hf * 16, pk);
               }
               fence_proxy_async_smem();
               __syncwarp();
               if (lane == 0) {
                 tma_store_2d(&tmO, sb, col + hf * 16, row0);
+                bulk_commit_group();
+              }
+            }
+            if constexpr (emit) {
+              // the chunk's bf16 copy (32 rows x 64 bytes: the geometry of an fp32 half) leaves the same way; thread-per-
+              // row 32-byte global stores cost the short-K attn.proj GEMM as much as the fp32 ones once did
+              if (lane == 0) bulk_wait_group_read<1>();
+              __syncwarp();
+              const uint32_t sb = sbuf + (sk++ & 1u) * 2048u;
+#pragma unroll
+              for (int j = 0; j < 4; ++j)
+                st_shared_v4(sb + srow + (((uint32_t)j ^ sx) << 4), __uint_as_float(pk[4 * j]), __uint_as_float(pk[4 * j + 1]),
+                             __uint_as_float(pk[4 * j + 2]), __uint_as_float(pk[4 * j + 3]));
+              fence_proxy_async_smem();
+              __syncwarp();
+              if (lane == 0) {
+                tma_store_2d(&tmX, sb, col, row0);
                 bulk_commit_group();
               }
             }
@@ -354,28 +385,13 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
           float s0, s1, q0, q1;
           f2_unpack(rs2, s0, s1);
           f2_unpack(rq2, q0, q1);
-          const int np = CSPLIT * tiles_n;
-          reinterpret_cast<float2*>(g.stats_out)[(size_t)m * np + n_blk * CSPLIT + half] = make_float2(s0 + s1, q0 + q1);
+          reinterpret_cast<float2*>(g.stats_out)[(size_t)(n_blk * CSPLIT + half) * g.M + m] = make_float2(s0 + s1, q0 + q1);
         }
       } else if constexpr (kSimple) {
         uint32_t v[32];
         float* f = reinterpret_cast<float*>(v);
-        // folded LayerNorm (gemm_args.h): out = rstd * acc + (-rstd * mean) * colsum + bias
-                constexpr bool fold = epi_is_fold(EPI);
-        uint64_t rstd2 = 0, nrm2 = 0;
-        if constexpr (fold) {
-          const float2* sp = reinterpret_cast<const float2*>(g.stats_in) + (size_t)(row_ok ? m : 0) * g.stats_np;
-          float s = 0.f, ss = 0.f;
-          for (int i = 0; i < g.stats_np; ++i) {
-            const float2 t = sp[i];
-            s += t.x; ss += t.y;
-          }
-          const float inv_k = 1.0f / (float)g.K;
-          const float mean = s * inv_k;
-          const float rstd = rsqrtf(fmaxf(ss * inv_k - mean * mean, 0.f) + g.fold_eps);
-          rstd2 = f2_pack(rstd, rstd);
-          nrm2 = f2_pack(-rstd * mean, -rstd * mean);
-        }
+        // folded LayerNorm: out = rstd * acc + (-rstd * mean) * colsum + bias
+        constexpr bool fold = epi_is_fold(EPI);
 #pragma unroll
         for (int ci = 0; ci < NCW; ++ci) {
           const int c = c_first + ci;

@@ -97,14 +97,14 @@ def test_producer_gemm_emits_stats_and_bf16_copy(M, N, K):
     ref = A.float() @ W.float().t() + bias + resid
     np_ = lib.inksam_op_gemm_stats_partials(N)
     assert np_ == 2 * ((N + 255) // 256)
-    st = torch.full((M, np_, 2), float("nan"), device="cuda")
+    st = torch.full((np_, M, 2), float("nan"), device="cuda")
     xb = torch.zeros(M, N, device="cuda", dtype=torch.bfloat16)
     out = resid.clone()
     gemm_fold(EPI["RESID"], A, W, out, bias=bias, resid=out, stats_out=st, xb_out=xb)
     assert rel_err(out, ref) < 2e-5
     assert torch.equal(xb, out.bfloat16())
-    assert rel_err(st[:, :, 0].sum(1), out.double().sum(1)) < 2e-5
-    assert rel_err(st[:, :, 1].sum(1), out.double().pow(2).sum(1)) < 2e-5
+    assert rel_err(st[:, :, 0].sum(0), out.double().sum(1)) < 2e-5
+    assert rel_err(st[:, :, 1].sum(0), out.double().pow(2).sum(1)) < 2e-5
     # without the side outputs the epilogue is the plain residual one
     out2 = resid.clone()
     gemm_fold(EPI["RESID"], A, W, out2, bias=bias, resid=out2)
@@ -122,7 +122,7 @@ def test_producer_gemm_emits_stats_and_bf16_copy(M, N, K):
 def test_gemm_fold_rejects_mismatched_arguments():
     lib = _lib.load()
     a = torch.zeros(256, 64, device="cuda", dtype=torch.bfloat16); w = torch.zeros(256, 64, device="cuda", dtype=torch.bfloat16)
-    o = torch.zeros(256, 256, device="cuda"); s = torch.zeros(256, 2, 2, device="cuda")
+    o = torch.zeros(256, 256, device="cuda"); s = torch.zeros(2, 256, 2, device="cuda")
     assert lib.inksam_op_gemm_fold(EPI["ROWADD"], ptr(a), 64, ptr(w), 64, 256, 256, 64, ptr(o), 256, None, None, None, None, None, None, 0,
                                    ctypes.c_float(1e-6), 0, stream()) != 0
     assert lib.inksam_op_gemm_fold(EPI["RESID"], ptr(a), 64, ptr(w), 64, 256, 256, 64, ptr(o), 256, None, ptr(o), None, None, ptr(s), None, 1,
