@@ -230,3 +230,25 @@ def test_sam_forward_batched_entry_matches_oracle():
     with pytest.raises(NotImplementedError):
         sam([dict(batch[0], point_coords=torch.zeros(1, 1, 2))], multimask_output=False)
     assert sam([], multimask_output=False) == []
+
+
+@pytest.mark.parametrize("offset", [1.25, 3.0])
+def test_encoder_parity_with_offset_token_means(offset):
+    """The LayerNorms of the encoder blocks are folded into the GEMMs around them, which rounds the raw
+    residual stream to bf16 instead of its normalised form: accuracy then depends on |mean| / std of a token row (0.05
+    with the synthetic weights, where the stream's std is 1.25).  A constant added to pos_embed moves every token's mean
+    to 1x / 2.4x its spread; the reference's LayerNorm removes it exactly, and the embeddings must stay inside the stated
+    tolerance (rel-RMS <= 1e-2 against the fp32 oracle)."""
+    cfg_name = "vit_tiny80"
+    sd = dict(synthetic_state_dict(CONFIGS[cfg_name], 5))
+    sd["image_encoder.pos_embed"] = sd["image_encoder.pos_embed"] + offset
+    from inklayer_b200.synth import synthetic_sketch
+    img = synthetic_sketch(2, 1024, 1024)
+    sam = build_sam_from_state_dict(sd, CONFIGS[cfg_name]).to("cuda")
+    pred = SamPredictor(sam)
+    pred.set_image(img)
+    ora = O.OraclePredictor(O.CONFIGS[cfg_name], sd)
+    ora.set_image(img)
+    err = rel_rms(pred.features.cpu(), ora.features)
+    print(f"pos_embed + {offset}: embedding rel-RMS {err:.2e}")
+    assert err <= 1e-2
