@@ -187,7 +187,7 @@ def run_b200(args):
     sizes = [size] * BATCH
 
     def step_resident():
-        feats = sam.encode(d_imgs, graph=True)  # the encoder's ~260 launches replay from a CUDA graph
+        feats = sam.encode(d_imgs, graph=True)  # the encoder's ~200 launches replay from a CUDA graph
         return sam.decode_batch(feats, d_boxes, sizes, sizes, masks_out=d_masks)
 
     def step_e2e(steps=1):

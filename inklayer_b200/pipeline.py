@@ -51,7 +51,7 @@ class SketchSegmenter:
     pass.  `depth` batches are in flight: the pinned-memory H2D copy of batch i+1 and the D2H copy + host hand-off of
     batch i-1 run on their own streams / a worker thread under the kernels of batch i."""
 
-    def __init__(self, sam: Sam, max_batch: int = 8, depth: int = 2) -> None:
+    def __init__(self, sam: Sam, max_batch: int = 8, depth: int = 2, copy_threads: int = 4) -> None:
         if sam.device.type != "cuda":
             raise RuntimeError("SketchSegmenter needs a Sam on a CUDA device")
         self.sam = sam
@@ -62,7 +62,7 @@ class SketchSegmenter:
         with torch.cuda.device(sam.device):
             self._s_in, self._s_run, self._s_out = torch.cuda.Stream(), torch.cuda.Stream(), torch.cuda.Stream()
         self._pool = ThreadPoolExecutor(max_workers=1)        # one hand-off per batch, in order
-        self._copy_pool = ThreadPoolExecutor(max_workers=4)   # per-image copies out of pinned memory (numpy drops the GIL)
+        self._copy_pool = ThreadPoolExecutor(max_workers=max(1, copy_threads))  # per-image copies out of pinned memory (numpy drops the GIL)
         self._next = 0
         self.h2d_bytes = 0
         self.d2h_bytes = 0
