@@ -193,6 +193,31 @@ def test_vit_l_matches_oracle():
     assert e <= 1e-2 and lo <= 1e-2 and ious.min() >= 0.99
 
 
+def test_vit_h_full_tensors_match_oracle():
+    """The flagship config on FULL tensors: the golden fixture of vit_h_1024 keeps every 4th low-res pixel (one phase of the
+    transposed convolutions, a noisy sub-sample: profiles/r01r_parity_variants.txt), so the whole embedding, every low-res
+    logit and every mask of another weight / sketch / box set are checked here against the CPU oracle run on this box."""
+    from inklayer_b200.synth import synthetic_boxes, synthetic_sketch
+
+    cfg_name = "vit_h"
+    sd = synthetic_state_dict(CONFIGS[cfg_name], 7)
+    img = synthetic_sketch(11, 1024, 1024)
+    boxes = torch.from_numpy(synthetic_boxes(11, 8, 1024, 1024))
+    sam = build_sam_from_state_dict(sd, CONFIGS[cfg_name]).to("cuda")
+    pred = SamPredictor(sam)
+    pred.set_image(img)
+    tb = pred.transform.apply_boxes_torch(boxes, img.shape[:2])
+    masks, iou, low = pred.predict_torch(None, None, boxes=tb.cuda(), multimask_output=False)
+    ora = O.OraclePredictor(O.CONFIGS[cfg_name], sd)
+    ora.set_image(img)
+    m_ref, i_ref, l_ref = ora.predict_torch(O.apply_boxes(boxes, img.shape[:2]))
+    e, lo = rel_rms(pred.features.cpu(), ora.features), rel_rms(low.cpu(), l_ref)
+    ious = mask_iou(masks.cpu().numpy(), m_ref.numpy())
+    print(f"vit_h (full tensors): emb rel-RMS {e:.2e}  low-res rel-RMS {lo:.2e}  min IoU {ious.min():.4f}")
+    assert e <= 1e-2 and lo <= 1e-2 and ious.min() >= 0.99
+    assert (iou.cpu() - i_ref).abs().max() < 2e-2
+
+
 def test_sam_forward_batched_entry_matches_oracle():
     """Sam.forward (modeling/sam.py:53-131): list-of-dicts in, list-of-dicts out, images of different input sizes in one
     batch; checked against the CPU oracle image by image, and the unsupported prompt kinds raise."""
