@@ -88,6 +88,17 @@ int inksam_decode_batch(inksam_handle* h, const float* embeddings, int B, const 
                         const int* in_hw, const int* orig_hw, uint8_t* masks_out, float* iou_out, float* lowres_out,
                         float* logits_out, float mask_threshold, void* stream);
 
+/* Workspace.  The library owns its workspace.  inksam_workspace_bytes: what encodes of up to max_batch
+ * images per call and decodes of up to max_batch images with up to max_boxes boxes in total need.  inksam_reserve sizes
+ * the workspace once for that envelope (synchronises the device; releases buffers retired by earlier growth) so that no
+ * later call inside it allocates -- CUDA graphs captured over inksam_encode stay valid.  A call outside the envelope
+ * grows the workspace WITHOUT a device synchronisation and without freeing the old buffer (it is retired until the next
+ * inksam_reserve / inksam_destroy) and increments inksam_workspace_generation: graphs captured under an older generation
+ * replay into retired memory and must be dropped by the caller. */
+size_t inksam_workspace_bytes(const inksam_handle* h, int max_batch, int max_boxes);
+int inksam_reserve(inksam_handle* h, int max_batch, int max_boxes);
+long long inksam_workspace_generation(const inksam_handle* h);
+
 /* Number of kernels this handle has launched so far (bench.py's gpu_launches). */
 long long inksam_launch_count(const inksam_handle* h);
 

@@ -33,6 +33,9 @@ SIGNATURES = {
                                     c_void_p, c_void_p, c_float, c_void_p]),
     "inksam_decode_batch": (c_int, [c_void_p, c_void_p, c_int, c_void_p, POINTER(c_int), POINTER(c_int), POINTER(c_int),
                                     c_void_p, c_void_p, c_void_p, c_void_p, c_float, c_void_p]),
+    "inksam_workspace_bytes": (c_size_t, [c_void_p, c_int, c_int]),
+    "inksam_reserve": (c_int, [c_void_p, c_int, c_int]),
+    "inksam_workspace_generation": (c_longlong, [c_void_p]),
     "inksam_launch_count": (c_longlong, [c_void_p]),
     "inksam_profile_enable": (c_int, [c_void_p, c_int]),
     "inksam_profile_read": (c_int, [c_void_p, POINTER(ctypes.c_double), POINTER(ctypes.c_double), POINTER(c_longlong)]),

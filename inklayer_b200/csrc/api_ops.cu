@@ -5,12 +5,9 @@
 using namespace inksam;
 
 static int device_sms() {
-  static int sms = 0;
-  if (sms == 0) {
-    int dev = 0;
-    cudaGetDevice(&dev);
-    cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
-  }
+  static PerDeviceInt sms_dev;
+  int& sms = sms_dev();
+  if (sms == 0) cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, current_device());
   return sms;
 }
 

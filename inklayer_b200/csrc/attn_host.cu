@@ -20,10 +20,10 @@ static int launch_global(const __nv_bfloat16* qkv, const __nv_bfloat16* rel, con
   }
   using L = AttnGlobal2<HD>;
   auto kern = attn_global2_kernel<HD>;
-  static bool attr_done = false;
-  if (!attr_done) {
+  static PerDeviceFlag attr_done;
+  if (!attr_done()) {
     CUDA_TRY(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, L::SMEM_BYTES));
-    attr_done = true;
+    attr_done() = true;
   }
   kern<<<a.B * a.heads * 16, L::THREADS, L::SMEM_BYTES, st>>>(tm64, tm16, tr64, tr16, a);
   CUDA_TRY(cudaGetLastError());
@@ -46,14 +46,13 @@ static int launch_window(const __nv_bfloat16* qkv, const __nv_bfloat16* rel, con
   }
   using L = AttnWindow2<HD>;
   auto kern = attn_window2_kernel<HD>;
-  static bool attr_done = false;
-  static int num_sms = 0;
-  if (!attr_done) {
+  static PerDeviceFlag attr_done;
+  static PerDeviceInt num_sms_dev;
+  int& num_sms = num_sms_dev();
+  if (!attr_done()) {
     CUDA_TRY(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, L::SMEM_BYTES));
-    int dev = 0;
-    CUDA_TRY(cudaGetDevice(&dev));
-    CUDA_TRY(cudaDeviceGetAttribute(&num_sms, cudaDevAttrMultiProcessorCount, dev));
-    attr_done = true;
+    CUDA_TRY(cudaDeviceGetAttribute(&num_sms, cudaDevAttrMultiProcessorCount, current_device()));
+    attr_done() = true;
   }
   const int items = a.B * 25 * a.heads * 2;
   const int pairs = items / 2;  // a CTA takes both row tiles of a (window, head) so that K and V are loaded once

@@ -26,6 +26,24 @@ const char* get_error();
     if ((expr) != 0) return -1;  \
   } while (0)
 
+// cudaFuncSetAttribute(MaxDynamicSharedMemorySize), cluster occupancy and the SM count are PER DEVICE: launchers keep their
+// "already configured" state in one of these, indexed by the calling thread's current device (one process may hold
+// handles on several GPUs: Sam.to('cuda:1') after 'cuda:0').
+constexpr int kMaxDevices = 64;
+inline int current_device() {
+  int d = 0;
+  cudaGetDevice(&d);
+  return (d >= 0 && d < kMaxDevices) ? d : 0;
+}
+struct PerDeviceFlag {
+  bool done[kMaxDevices] = {};
+  bool& operator()() { return done[current_device()]; }
+};
+struct PerDeviceInt {
+  int v[kMaxDevices] = {};
+  int& operator()() { return v[current_device()]; }
+};
+
 int make_tmap_bf16_box(CUtensorMap* out, const void* base, uint64_t rows, uint64_t cols, uint64_t ld_elems,
                        uint32_t box_cols, uint32_t box_rows);
 

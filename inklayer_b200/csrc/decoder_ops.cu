@@ -242,10 +242,10 @@ __global__ void __launch_bounds__(TOK_THREADS, 1) decoder_token_kernel(const Dec
 
 int launch_decoder_tokens(const DecWeights& w, const DecState& s, int boxes, int phase, int layer, cudaStream_t st) {
   constexpr int SMEM = (5 * NT * E + NT * 2048) * 4;
-  static bool attr_done = false;
-  if (!attr_done) {
+  static PerDeviceFlag attr_done;
+  if (!attr_done()) {
     CUDA_TRY(cudaFuncSetAttribute(decoder_token_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM));
-    attr_done = true;
+    attr_done() = true;
   }
   decoder_token_kernel<<<boxes, TOK_THREADS, SMEM, st>>>(w, s, phase, layer);
   CUDA_TRY(cudaGetLastError());

@@ -45,9 +45,14 @@ struct inksam_handle {
   float *pe = nullptr;                       // dense PE, token-major [4096][256]
   float *wkvq[2] = {nullptr, nullptr}, *bkvq[2] = {nullptr, nullptr}, *ra[2] = {nullptr, nullptr};  // [384][256], [384], [4096][384]
   float *wkvf = nullptr, *bkvf = nullptr, *raf = nullptr;                                            // [256][256], [256], [4096][256]
-  // workspaces (grow-only)
+  // workspaces: sized once by inksam_reserve, otherwise grow-only.  A buffer that has to grow is RETIRED, not freed (work
+  // already enqueued on any stream -- or baked into a captured CUDA graph -- may still use it); retired buffers are released
+  // by inksam_reserve / inksam_destroy after a device synchronisation.  ws_generation counts reallocations so that the
+  // caller can drop graphs that hold pointers into a retired buffer.
   void* enc_ws = nullptr; size_t enc_ws_bytes = 0;
   void* dec_ws = nullptr; size_t dec_ws_bytes = 0;
+  std::vector<void*> retired;
+  long long ws_generation = 0;
   // optional per-category CUDA-event timing of the launches (bench.py's roofline numbers)
   bool prof_on = false;
   int prof_cat = 0;  // category the next launches are charged to (offset by 3 inside decode)
@@ -70,11 +75,31 @@ int dev_alloc(inksam_handle* h, void** p, size_t bytes) {
   return 0;
 }
 
-int grow(void** p, size_t* have, size_t need) {
+// No device synchronisation and no cudaFree on this path: see the comment on inksam_handle::retired.
+int grow(inksam_handle* h, void** p, size_t* have, size_t need) {
   if (need <= *have) return 0;
-  if (*p) { CUDA_TRY(cudaDeviceSynchronize()); CUDA_TRY(cudaFree(*p)); *p = nullptr; *have = 0; }
-  CUDA_TRY(cudaMalloc(p, need));
-  *have = need;
+  size_t want = need;
+  if (*p) {
+    h->retired.push_back(*p);
+    *p = nullptr;
+    if (want < *have + *have / 2) want = *have + *have / 2;  // geometric: retired memory stays below 2x the live buffer
+    *have = 0;
+  }
+  if (cudaMalloc(p, want) != cudaSuccess) {
+    (void)cudaGetLastError();
+    CUDA_TRY(cudaMalloc(p, need));
+    want = need;
+  }
+  *have = want;
+  ++h->ws_generation;
+  return 0;
+}
+
+int release_retired(inksam_handle* h) {
+  if (h->retired.empty()) return 0;
+  CUDA_TRY(cudaDeviceSynchronize());
+  for (void* q : h->retired) cudaFree(q);
+  h->retired.clear();
   return 0;
 }
 
@@ -165,6 +190,7 @@ void inksam_destroy(inksam_handle* h) {
   cudaDeviceSynchronize();
   for (auto& kv : h->w) cudaFree(kv.second.p);
   for (void* p : h->owned) cudaFree(p);
+  for (void* p : h->retired) cudaFree(p);
   if (h->enc_ws) cudaFree(h->enc_ws);
   if (h->dec_ws) cudaFree(h->dec_ws);
   delete h;
@@ -395,28 +421,38 @@ namespace {
 
 size_t align_up(size_t x) { return (x + 1023) & ~size_t(1023); }
 
+// Carve-up of the encoder workspace for a chunk of B images (offsets in bytes).
+struct EncLayout { size_t x, xn, qkv, attn, hp, pad, stats, total; };
+EncLayout enc_layout(const inksam_handle* h, int B) {
+  const int D = h->cfg.embed_dim;
+  const size_t M = (size_t)B * 4096, WROWS = (size_t)B * 25 * 196;  // window-ordered rows (>= M)
+  const size_t sz_x = align_up(M * D * 4), sz_xn = align_up(M * D * 2);
+  const size_t sz_qkv = align_up(WROWS * 3 * D * 2), sz_attn = sz_xn, sz_h = align_up(M * 4 * D * 2);
+  const size_t sz_pad = align_up((size_t)B * 66 * 66 * 256 * 2);
+  const size_t sz_patch = align_up(M * 768 * 2);
+  const size_t sz_hp = sz_h > sz_patch ? sz_h : sz_patch;  // patches alias the MLP hidden buffer
+  const size_t sz_stats = align_up(M * gemm_stats_partials(D) * 2 * 4);  // partial row statistics of the proj / lin2 epilogues
+  EncLayout L;
+  L.x = 0; L.xn = L.x + sz_x; L.qkv = L.xn + sz_xn; L.attn = L.qkv + sz_qkv; L.hp = L.attn + sz_attn; L.pad = L.hp + sz_hp;
+  L.stats = L.pad + sz_pad; L.total = L.stats + sz_stats;
+  return L;
+}
+
 int encode_chunk(inksam_handle* h, const void* images, int dtype, int B, const int* hw, long long img_stride,
                  long long row_pitch, long long plane_stride, float* emb_out, cudaStream_t st) {
   const int D = h->cfg.embed_dim, heads = h->cfg.num_heads, hd = h->head_dim;
   const int M = B * 4096;
-  const size_t WROWS = (size_t)B * 25 * 196;  // window-ordered rows (>= M)
-  // workspace carve-up
-  const size_t sz_x = align_up((size_t)M * D * 4), sz_xn = align_up((size_t)M * D * 2);
-  const size_t sz_qkv = align_up(WROWS * 3 * D * 2), sz_attn = sz_xn, sz_h = align_up((size_t)M * 4 * D * 2);
-  const size_t sz_pad = align_up((size_t)B * 66 * 66 * 256 * 2);
-  const size_t sz_patch = align_up((size_t)M * 768 * 2);
-  const size_t sz_hp = sz_h > sz_patch ? sz_h : sz_patch;  // patches alias the MLP hidden buffer
   const int np = gemm_stats_partials(D);  // partial row statistics written by the proj / lin2 epilogues
-  const size_t sz_stats = align_up((size_t)M * np * 2 * 4);
-  INK_TRY(grow(&h->enc_ws, &h->enc_ws_bytes, sz_x + sz_xn + sz_qkv + sz_attn + sz_hp + sz_pad + sz_stats));
+  const EncLayout L = enc_layout(h, B);
+  INK_TRY(grow(h, &h->enc_ws, &h->enc_ws_bytes, L.total));
   char* base = static_cast<char*>(h->enc_ws);
-  float* x = reinterpret_cast<float*>(base);
-  void* xn = base + sz_x;
-  void* qkv = base + sz_x + sz_xn;
-  void* attn = base + sz_x + sz_xn + sz_qkv;
-  void* hbuf = base + sz_x + sz_xn + sz_qkv + sz_attn;
-  void* pad = base + sz_x + sz_xn + sz_qkv + sz_attn + sz_hp;
-  float* stats = reinterpret_cast<float*>(base + sz_x + sz_xn + sz_qkv + sz_attn + sz_hp + sz_pad);
+  float* x = reinterpret_cast<float*>(base + L.x);
+  void* xn = base + L.xn;
+  void* qkv = base + L.qkv;
+  void* attn = base + L.attn;
+  void* hbuf = base + L.hp;
+  void* pad = base + L.pad;
+  float* stats = reinterpret_cast<float*>(base + L.stats);
 
   const float *pos, *patch_b, *n1w, *n1b, *n3w, *n3b;
   const void *patch_w, *neck0, *neck2;
@@ -521,6 +557,21 @@ extern "C" int inksam_encode(inksam_handle* h, const void* images, int dtype, in
 namespace {
 
 constexpr int kBoxChunk = 128;  // boxes decoded per pass (bounds the workspace at ~2.2 GB)
+
+// Decoder workspace for B images with K boxes in total: per-image layer-0 keys and their merged projection, the image
+// index of every box, then the buffers of one chunk of at most kBoxChunk boxes (carved up by decode_chunk).
+struct DecLayout { size_t kvq0, idx, shared, total; };
+DecLayout dec_layout(int B, int K) {
+  const int nc = K < kBoxChunk ? K : kBoxChunk;
+  const size_t sz_keys0 = align_up((size_t)B * 4096 * 256 * 4), sz_kvq0 = align_up((size_t)B * 4096 * 384 * 4);
+  const size_t sz_idx = align_up((size_t)K * 4);
+  const size_t chunk_bytes = align_up((size_t)nc * 4096 * 256 * 4) + align_up((size_t)nc * 4096 * 384 * 4) +
+                             align_up((size_t)nc * 4096 * 128 * 4) + 8 * align_up((size_t)nc * 7 * 256 * 4) +
+                             align_up(decoder_t2i_scratch_floats(nc) * 4) + align_up((size_t)nc * 4);
+  DecLayout L;
+  L.kvq0 = sz_keys0; L.idx = sz_keys0 + sz_kvq0; L.shared = sz_keys0 + sz_kvq0 + sz_idx; L.total = L.shared + chunk_bytes;
+  return L;
+}
 
 // Per-image geometry of a decode batch (host side).
 struct ImgGeom { int in_h, in_w, H, W; size_t mask_off; };  // mask_off: element offset of the image's first mask
@@ -681,18 +732,13 @@ extern "C" int inksam_decode_batch(inksam_handle* h, const float* embeddings, in
   CUDA_TRY(cudaSetDevice(h->device));
   auto st = static_cast<cudaStream_t>(stream);
   struct CatGuard { inksam_handle* h; CatGuard(inksam_handle* x) : h(x) { h->prof_cat = 1; } ~CatGuard() { h->prof_cat = 0; } } guard(h);
-  const int nc = K < kBoxChunk ? K : kBoxChunk;
-  const size_t sz_keys0 = align_up((size_t)B * 4096 * 256 * 4), sz_kvq0 = align_up((size_t)B * 4096 * 384 * 4);
-  const size_t sz_idx = align_up((size_t)K * 4);
-  const size_t shared_bytes = sz_keys0 + sz_kvq0 + sz_idx;
-  const size_t chunk_bytes = align_up((size_t)nc * 4096 * 256 * 4) + align_up((size_t)nc * 4096 * 384 * 4) +
-                             align_up((size_t)nc * 4096 * 128 * 4) + 8 * align_up((size_t)nc * 7 * 256 * 4) +
-                             align_up(decoder_t2i_scratch_floats(nc) * 4) + align_up((size_t)nc * 4);
-  INK_TRY(grow(&h->dec_ws, &h->dec_ws_bytes, shared_bytes + chunk_bytes));
+  const DecLayout L = dec_layout(B, K);
+  const size_t shared_bytes = L.shared;
+  INK_TRY(grow(h, &h->dec_ws, &h->dec_ws_bytes, L.total));
   char* ws = static_cast<char*>(h->dec_ws);
   float* keys0 = reinterpret_cast<float*>(ws);
-  float* kvq0 = reinterpret_cast<float*>(ws + sz_keys0);
-  int* box_img = reinterpret_cast<int*>(ws + sz_keys0 + sz_kvq0);
+  float* kvq0 = reinterpret_cast<float*>(ws + L.kvq0);
+  int* box_img = reinterpret_cast<int*>(ws + L.idx);
   const float* nomask = nullptr;
   INK_TRY(need_f32(h, "prompt_encoder.no_mask_embed.weight", &nomask));
   ++h->launches;
@@ -722,6 +768,30 @@ extern "C" int inksam_decode_boxes(inksam_handle* h, const float* embedding, con
   return inksam_decode_batch(h, embedding, 1, boxes, counts, in_hw, orig_hw, masks_out, iou_out, lowres_out, logits_out,
                              mask_threshold, stream);
 }
+
+// ================================================================================================ workspace
+// Bytes of library-owned workspace that encodes of up to max_batch images per call (per chunk of 32) and decodes of up to
+// max_batch images with up to max_boxes boxes in total need.
+extern "C" size_t inksam_workspace_bytes(const inksam_handle* h, int max_batch, int max_boxes) {
+  if (!h || max_batch < 1 || max_boxes < 0) return 0;
+  const int eb = max_batch < 32 ? max_batch : 32, db = max_batch < kMaxDecodeImages ? max_batch : kMaxDecodeImages;
+  return enc_layout(h, eb).total + (max_boxes > 0 ? dec_layout(db, max_boxes).total : 0);
+}
+
+// Sizes both workspaces once for that envelope, so that no later call inside it allocates (a captured CUDA graph keeps
+// pointing at live memory), and releases buffers retired by earlier growth.  Synchronises the device.
+extern "C" int inksam_reserve(inksam_handle* h, int max_batch, int max_boxes) {
+  if (!h) return set_error("inksam_reserve: null handle");
+  if (max_batch < 1 || max_boxes < 0) return set_error("inksam_reserve: max_batch %d / max_boxes %d", max_batch, max_boxes);
+  CUDA_TRY(cudaSetDevice(h->device));
+  const int eb = max_batch < 32 ? max_batch : 32, db = max_batch < kMaxDecodeImages ? max_batch : kMaxDecodeImages;
+  INK_TRY(grow(h, &h->enc_ws, &h->enc_ws_bytes, enc_layout(h, eb).total));
+  if (max_boxes > 0) INK_TRY(grow(h, &h->dec_ws, &h->dec_ws_bytes, dec_layout(db, max_boxes).total));
+  return release_retired(h);
+}
+
+// Incremented whenever a workspace buffer is reallocated: graphs captured under an older generation must be dropped.
+extern "C" long long inksam_workspace_generation(const inksam_handle* h) { return h ? h->ws_generation : 0; }
 
 // ================================================================================================ profiling
 extern "C" int inksam_profile_enable(inksam_handle* h, int on) {

@@ -107,10 +107,10 @@ static int launch_one(const CUtensorMap& tA, const CUtensorMap& tB, const CUtens
                       cudaStream_t st) {
   using C = GemmCfg<CG, TF32, BN, gemm_staged(EPI)>;
   auto kern = gemm_tc_kernel<CG, TF32, BN, EPI>;
-  static bool attr_done = false;
-  if (!attr_done) {
+  static PerDeviceFlag attr_done;  // per device (and per instantiation)
+  if (!attr_done()) {
     CUDA_TRY(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, C::SMEM_BYTES));
-    attr_done = true;
+    attr_done() = true;
   }
   const int tiles = ((g.M + C::BM * CG - 1) / (C::BM * CG)) * ((g.N + BN - 1) / BN);
   cudaLaunchConfig_t cfg{};
@@ -130,7 +130,8 @@ static int launch_one(const CUtensorMap& tA, const CUtensorMap& tB, const CUtens
   cfg.numAttrs = 2;
   // The tile loop is statically strided over the resident clusters, so the grid must not exceed what is
   // co-resident: CTA pairs need both SMs of a TPC, and not every SM of the 148 can be paired on every part.
-  static int max_clusters = 0;
+  static PerDeviceInt max_clusters_dev;
+  int& max_clusters = max_clusters_dev();
   if (max_clusters == 0) {
     max_clusters = num_sms / CG;
     if (CG > 1) {

@@ -124,12 +124,13 @@ def run_directory(directory: str, out_dir: str, boxes_fn: BoxesFn, segmenter=Non
     if segmenter is None:
         import torch
 
-        from .pipeline import SketchSegmenter
-        from .sam import build_sam
+        from .pipeline import default_ckpt, segmenter_for_checkpoint
 
         local = int(os.environ.get("LOCAL_RANK", "0"))
         torch.cuda.set_device(local)
-        segmenter = SketchSegmenter(build_sam(os.environ.get("INKSAM_CHECKPOINT")).to(torch.device("cuda", local)))
+        # a missing checkpoint raises (InkLayer/segmentor/sam.py:17-19 stops there too); never synthetic weights
+        segmenter = segmenter_for_checkpoint(os.environ.get("INKSAM_CHECKPOINT", default_ckpt), torch.device("cuda", local),
+                                             max_batch=8)
     local_res = segment_shard(paths, boxes_fn, segmenter, rank, world)
     if write:
         for i, masks in local_res.items():

@@ -170,19 +170,44 @@ class SketchSegmenter:
         return out
 
 
-_default: Optional[SketchSegmenter] = None
+def get_model_path(filename: str) -> str:
+    """InkLayer/utils/paths.py:4-6 resolves `<InkLayer checkout>/models/<filename>`; this package is not inside that
+    checkout, so the directory is `$INKLAYER_MODELS` when set, else `./models`."""
+    import os
+
+    return os.path.join(os.environ.get("INKLAYER_MODELS", "models"), filename)
+
+
+default_ckpt = get_model_path("sam_vit_h_4b8939.pth")  # InkLayer/segmentor/sam.py:13
+_segmenters: dict = {}  # absolute checkpoint path -> SketchSegmenter (the reference rebuilds the model on every call)
+
+
+def segmenter_for_checkpoint(sam_checkpoint: str, device="cuda", max_batch: int = 1) -> SketchSegmenter:
+    """The cached segmenter of one checkpoint file.  A missing file raises: the reference stops in `breakpoint()` there
+    (segmentor/sam.py:17-19); there is no silent fall-back to synthetic weights (tests and bench.py build those explicitly
+    with build_sam_from_state_dict(synthetic_state_dict(...)) and pass `segmenter=`)."""
+    import os
+
+    if sam_checkpoint is None or not os.path.exists(sam_checkpoint):
+        raise FileNotFoundError(f"Checkpoint not found at {sam_checkpoint}")
+    key = (os.path.abspath(sam_checkpoint), str(device), max_batch)
+    seg = _segmenters.get(key)
+    if seg is None:
+        seg = SketchSegmenter(build_sam(checkpoint=sam_checkpoint).to(device), max_batch=max_batch)
+        _segmenters[key] = seg
+    return seg
 
 
 def run_SAM(image_pil, boxes_filt, sam_checkpoint: Optional[str] = None, segmenter: Optional[SketchSegmenter] = None):
     """Drop-in for InkLayer/segmentor/sam.py:16-43.  image_pil: PIL RGB image; boxes_filt: float tensor/array [K,4]
-    pixel xyxy.  Returns a list of K bool arrays [H,W] (or the reference's 2-tuple of empty arrays for K == 0)."""
-    global _default
+    pixel xyxy (InkLayer/utils/processing.py:6-28).  Returns a list of K np.bool_ arrays [H,W], or the reference's 2-tuple
+    of empty arrays for K == 0 (sam.py:20-21).  `sam_checkpoint` defaults to `default_ckpt` like the reference's; the
+    model of a checkpoint is built once and kept, not rebuilt per image.  `segmenter` (an extension) supplies an already
+    built SketchSegmenter instead of a checkpoint."""
+    if segmenter is None:
+        segmenter = segmenter_for_checkpoint(default_ckpt if sam_checkpoint is None else sam_checkpoint)
     if len(boxes_filt) == 0:
         return np.array([]), np.array([])
-    if segmenter is None:
-        if _default is None:
-            _default = SketchSegmenter(build_sam(checkpoint=sam_checkpoint).to("cuda"), max_batch=1)
-        segmenter = _default
     image = np.array(image_pil)[..., ::-1]  # the reference applies COLOR_BGR2RGB to an RGB array (sam.py:24-25)
     bx = boxes_filt.detach().cpu().numpy() if isinstance(boxes_filt, torch.Tensor) else np.asarray(boxes_filt)
     masks = segmenter.segment_batch([np.ascontiguousarray(image)], [bx])[0]

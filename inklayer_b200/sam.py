@@ -39,6 +39,7 @@ class Sam:
         self._graphs: dict = {}        # encode() CUDA graphs: key -> (graph, output, input, kernel launches per replay)
         self._graph_seen: dict = {}
         self._graph_launches = 0       # kernels launched by graph replays (the library counts stream launches only)
+        self._graph_gen = 0            # inksam_workspace_generation the cached graphs were captured under
         self._profiling = False
 
     # ------------------------------------------------------------------ weights
@@ -128,6 +129,25 @@ class Sam:
     def launch_count(self) -> int:
         return int(_lib.load().inksam_launch_count(self._require())) + self._graph_launches
 
+    def reserve(self, max_batch: int, max_boxes: int = 128) -> int:
+        """Sizes the library's workspace once for encodes of up to `max_batch` images and decodes of up to `max_boxes`
+        boxes per pass (inksam_reserve): nothing inside that envelope allocates afterwards, so CUDA graphs captured by
+        encode(graph=True) stay valid.  Synchronises the device.  Returns the workspace size in bytes."""
+        lib = _lib.load()
+        with torch.cuda.device(self.device):
+            _lib.check(lib.inksam_reserve(self._require(), int(max_batch), int(max_boxes)))
+        self._drop_stale_graphs()
+        return int(lib.inksam_workspace_bytes(self._require(), int(max_batch), int(max_boxes)))
+
+    def _drop_stale_graphs(self) -> None:
+        """Graphs bake in pointers into the library's workspace: when it was reallocated since they were captured
+        (inksam_workspace_generation moved) they would replay into retired memory, so they are dropped and re-captured."""
+        gen = int(_lib.load().inksam_workspace_generation(self._require()))
+        if gen != self._graph_gen:
+            self._graphs.clear()
+            self._graph_seen.clear()
+            self._graph_gen = gen
+
     def profile(self, on: bool) -> None:
         """Start (and reset) / stop per-category CUDA-event timing of the library's launches."""
         _lib.check(_lib.load().inksam_profile_enable(self._require(), 1 if on else 0))
@@ -178,6 +198,7 @@ class Sam:
                                                      _ptr(out), _stream(self.device)))
 
         if graph and not self._profiling:
+            self._drop_stale_graphs()
             key = (images.data_ptr(), dtype, B, hh, ww, tuple(hw))
             hit = self._graphs.get(key)
             if hit is not None:
@@ -190,6 +211,7 @@ class Sam:
                 n0 = int(_lib.load().inksam_launch_count(self._require()))
                 run(out)  # workspaces are grown outside the capture
                 per_replay = int(_lib.load().inksam_launch_count(self._require())) - n0
+                self._drop_stale_graphs()  # that run may have grown the workspace under older graphs
                 g = torch.cuda.CUDAGraph()
                 # thread_local: SketchSegmenter's hand-off thread may be waiting on events / copying while this captures
                 with torch.cuda.graph(g, capture_error_mode="thread_local"):
@@ -342,7 +364,7 @@ def _build(name: str, checkpoint: Optional[str]) -> Sam:
     sam = Sam(cfg)
     if checkpoint is not None:
         with open(checkpoint, "rb") as f:
-            sd = torch.load(f, map_location="cpu")
+            sd = torch.load(f, map_location="cpu", weights_only=True)  # a state_dict of tensors, never pickled code
         sam.load_state_dict(sd)
     else:
         # The reference returns torch's default random init here; there are no nn.Modules to initialise in this

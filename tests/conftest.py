@@ -20,24 +20,17 @@ def load_golden(name):
 
 def golden_case_inputs(name):
     """Same seeded inputs tests/golden/make_golden.py used (config name, weight seed, image, boxes)."""
-    import json
+    if GOLDEN not in sys.path:
+        sys.path.insert(0, GOLDEN)
+    from cases import case_inputs
 
-    from inklayer_b200.synth import synthetic_boxes, synthetic_sketch
+    return case_inputs(name)
 
-    cases = {
-        "tiny_1024": ("vit_tiny", 0, 0, (1024, 1024), 4),
-        "tiny80_600x750": ("vit_tiny80", 1, 1, (600, 750), 4),
-        "vit_b_750_bunny": ("vit_b", 0, 2, (750, 750), "bunny"),
-        "vit_h_1024": ("vit_h", 0, 3, (1024, 1024), 4),
-    }
-    cfg_name, seed, idx, (H, W), nb = cases[name]
-    img = synthetic_sketch(idx, H, W)
-    if nb == "bunny":
-        bunny = json.load(open(os.path.join(GOLDEN, "bunny_boxes.json")))["bboxes"][:16]
-        boxes = np.array(bunny, np.float32) * np.array([W, H, W, H], np.float32)
-    else:
-        boxes = synthetic_boxes(idx, nb, H, W)
-    return cfg_name, seed, img, boxes
+
+def golden_masks(gold):
+    """All K reference masks of a golden case as bool [K,1,H,W]."""
+    shape = tuple(int(v) for v in gold["mask_shape"])
+    return np.unpackbits(gold["mask_bits"])[: int(np.prod(shape))].reshape(shape).astype(bool)
 
 
 def mask_iou(a, b):
