@@ -1,16 +1,23 @@
 """Benchmark of the SAM segmentation hot path on B200 (BASELINE.json: sketches/sec, 1024^2 ViT-H encode + all-box decode).
 
-    python bench.py --gpus N --steps K --warmup W            # this implementation, one rank per GPU
-    python bench.py --impl reference --steps K --warmup W    # the reference algorithm on the host cores (oracle port)
+    python bench.py --gpus N --steps K --warmup W            # this implementation, one rank per GPU (torchrun for N > 1)
+    python bench.py --impl reference --steps K --warmup W    # the reference's own CPU code on the host cores
+    python bench.py --config 3 | 4 | 5                       # the other BASELINE.json configurations, one JSON line each
 
 A step = one batch of 8 synthetic 1024x1024 sketches per GPU: ViT-H image encoder on the batch, then the mask
 decoder + fused post-process on 16 boxes of every sketch (config 4 of BASELINE.json at per-step granularity;
 config 2 is its encoder part).  Prints ONE JSON line (rank 0).
-  value      sketches/s with inputs resident in HBM (CUDA events, max over ranks)
-  e2e        sketches/s through the public API (SketchSegmenter.segment_batch) from pinned host images to host masks
+  value      sketches/s with inputs resident in HBM (CUDA events around exactly K steps, max over ranks)
+  e2e        sketches/s through the public API (driver.segment_shard -> SketchSegmenter.segment_stream): >= 512 DISTINCT
+             host sketches per rank (global index g = rank + i * world, seeds 1000 + g / 3000 + g), host
+             boxes in, host masks out (bit-packed rows, the PIL mode "1" layout InkLayer/runner.py:51 converts to); pinned
+             H2D and D2H inside the timed region
+  parity     masks the e2e leg returned for global sketch 0 against the UNMODIFIED reference's masks for the same weights,
+             sketch and boxes (tests/golden/vit_h_bench0.npz); the run fails below IoU 0.99
   roofline   the dominant kernel (tcgen05 GEMM, every encoder instantiation): algorithmic 2*M*N*K per launch over the
              CUDA-event duration of those launches inside the timed steps, against the measured sustained bf16 peak
-  cpu_baseline   the oracle (CPU restatement of the reference) timed on this box's host cores on a bounded sample
+  decoder    HBM GB/s of a decode pass (ncu DRAM bytes of the pass / its live CUDA-event time) against the measured HBM peak
+  cpu_baseline   the reference (oracle/_ref, else the oracle port) timed on this box's host cores on a bounded sample
 """
 from __future__ import annotations
 
@@ -29,6 +36,7 @@ if ROOT not in sys.path:
 BATCH = 8           # sketches per step per GPU
 BOXES = 16          # boxes per sketch
 MODEL = "vit_h"
+E2E_MIN_BATCHES = 64  # the e2e leg streams at least 64 x 8 = 512 distinct sketches per rank
 ENC_GFLOP = {"vit_h": 5641.8, "vit_l": 2837.0, "vit_b": 937.6}  # algorithmic, SURVEY.md 8(d)
 METRIC = "sketches/sec (1024^2 ViT-H encode + all-box decode)"
 
@@ -38,16 +46,15 @@ def measured_peaks():
     if os.path.exists(p):
         d = json.load(open(p))
         return d.get("bf16_tflops_sustained", 1400.0), d.get("hbm_gbs", 6650.0), "measured"
-    return 1400.0, 6650.0, "fallback"
+    return 1400.0, 6650.0, "fallback (B200_PROFILING.md)"
 
 
-def gemm_traffic():
-    """DRAM bytes per encoder-GEMM launch from the committed `ncu --set full` capture (tools/ncu_summary.py traffic);
-    None if no capture has been summarised."""
-    p = os.path.join(ROOT, "profiles", "gemm_traffic.json")
+def committed_traffic(name: str, key: str):
+    """DRAM bytes from the committed `ncu --set full` capture (tools/ncu_summary.py); None if none has been summarised."""
+    p = os.path.join(ROOT, "profiles", name)
     if not os.path.exists(p):
         return None
-    return json.load(open(p)).get("dram_bytes_per_launch")
+    return json.load(open(p)).get(key)
 
 
 class ClockSampler:
@@ -82,88 +89,117 @@ class ClockSampler:
                 "samples": len(sm)}
 
 
-def synth_inputs(rank: int, n: int):
-    import numpy as np
+def synth_many(indices, boxes_per=BOXES, hw=(1024, 1024)):
+    """Sketches / boxes of the given GLOBAL indices (seeds 1000 + g and 3000 + g), generated on a few host threads."""
+    from concurrent.futures import ThreadPoolExecutor
 
     from inklayer_b200.synth import synthetic_boxes, synthetic_sketch
 
-    imgs = [synthetic_sketch(rank * 1000 + i) for i in range(n)]
-    boxes = [synthetic_boxes(rank * 1000 + i, BOXES) for i in range(n)]
-    return imgs, boxes, np
+    with ThreadPoolExecutor(max_workers=min(8, os.cpu_count() or 1)) as ex:
+        imgs = list(ex.map(lambda g: synthetic_sketch(g, hw[0], hw[1]), indices))
+    return imgs, [synthetic_boxes(g, boxes_per, hw[0], hw[1]) for g in indices]
 
 
-# ------------------------------------------------------------------------------------------------ reference arm
+def golden_masks(name: str):
+    import numpy as np
+
+    g = np.load(os.path.join(ROOT, "tests", "golden", name + ".npz"))
+    shape = tuple(int(v) for v in g["mask_shape"])
+    return np.unpackbits(g["mask_bits"])[: int(np.prod(shape))].reshape(shape).astype(bool), g["boxes"]
+
+
+def mask_ious(a, b):
+    import numpy as np
+
+    a, b = a.reshape(a.shape[0], -1), b.reshape(b.shape[0], -1)
+    inter, union = (a & b).sum(1).astype(np.float64), (a | b).sum(1).astype(np.float64)
+    return np.where(union > 0, inter / np.maximum(union, 1), 1.0)
+
+
+# ------------------------------------------------------------------------------------------------ the CPU arms
+class CpuArm:
+    """One ViT-H sketch with 16 boxes (set_image + predict_torch, fp32) on the host cores: the UNMODIFIED reference
+    (vendored segment_anything copied to oracle/_ref by oracle/install_ref.py: SA/predictor.py:34-60,168-243) when it is
+    present, else the oracle port (oracle/sam_oracle.py, pinned to the reference by tests/golden)."""
+
+    def __init__(self):
+        import torch
+
+        from inklayer_b200.config import CONFIGS
+        from inklayer_b200.weights import synthetic_state_dict
+        from oracle import ref_loader
+
+        self.cores = os.cpu_count() or 1
+        torch.set_num_threads(self.cores)
+        self.torch = torch
+        (self.img,), (self.boxes,) = synth_many([0])
+        sd = synthetic_state_dict(CONFIGS[MODEL], 0)
+        if ref_loader.available():
+            self.kind = "reference"
+            self.pred = ref_loader.reference_predictor(CONFIGS[MODEL], sd)
+            self.what = "unmodified vendored segment_anything (oracle/_ref): SamPredictor.set_image + predict_torch"
+        else:
+            from oracle import sam_oracle as O
+
+            self.kind = "port"
+            self.O = O
+            self.pred = O.OraclePredictor(O.CONFIGS[MODEL], sd)
+            self.what = "oracle/sam_oracle.py (CPU port pinned to the reference by tests/golden; oracle/_ref absent)"
+
+    def one(self):
+        """-> (seconds, masks bool [16,1,1024,1024])"""
+        torch = self.torch
+        t0 = time.perf_counter()
+        with torch.no_grad():
+            self.pred.set_image(self.img)
+            if self.kind == "reference":
+                tb = self.pred.transform.apply_boxes_torch(torch.from_numpy(self.boxes), self.img.shape[:2])
+                masks, _, _ = self.pred.predict_torch(None, None, boxes=tb, multimask_output=False)
+            else:
+                masks, _, _ = self.pred.predict_torch(self.O.apply_boxes(torch.from_numpy(self.boxes), self.img.shape[:2]))
+        return time.perf_counter() - t0, masks.numpy()
+
+
 def run_reference(args):
-    """The reference's own algorithm on the host cores: oracle/sam_oracle.py, the CPU restatement pinned to the
-    vendored segment_anything by tests/golden (the reference tree itself is not present on the GPU box).
+    """`--impl reference`: the reference's own CPU implementation of the path on the box's host cores, all threads.
     Each step = ONE sketch of the workload (ViT-H fp32, 16 boxes), bounded so the run ends within a few minutes."""
     rank = int(os.environ.get("RANK", "0"))
     if rank != 0:
         return
-    import torch
-
-    from inklayer_b200.config import CONFIGS
-    from inklayer_b200.weights import synthetic_state_dict
-    from oracle import sam_oracle as O
-
-    cores = os.cpu_count() or 1
-    torch.set_num_threads(cores)
-    imgs, boxes, np = synth_inputs(0, 1)
-    pred = O.OraclePredictor(O.CONFIGS[MODEL], synthetic_state_dict(CONFIGS[MODEL], 0))
-
-    def one():
-        t0 = time.perf_counter()
-        pred.set_image(imgs[0])
-        tb = O.apply_boxes(torch.from_numpy(boxes[0]), imgs[0].shape[:2])
-        pred.predict_torch(tb)
-        return time.perf_counter() - t0
-
-    warm = min(args.warmup, 1)
-    t_w = [one() for _ in range(warm)]
-    est = t_w[0] if t_w else 20.0
-    steps = max(1, min(args.steps, int(150.0 / max(est, 1e-3))))
-    ts = [one() for _ in range(steps)]
+    arm = CpuArm()
+    warm = max(1, min(args.warmup, 1))
+    t_w = [arm.one()[0] for _ in range(warm)]
+    steps = max(1, min(args.steps, int(150.0 / max(t_w[0], 1e-3))))
+    ts = [arm.one()[0] for _ in range(steps)]
     v = steps / sum(ts)
-    sample = f"{steps} step(s) of 1 sketch each (ViT-H fp32, {BOXES} boxes), {warm} warm-up; torch CPU ops, {cores} threads"
+    sample = (f"{steps} step(s) of 1 sketch each (ViT-H fp32, {BOXES} boxes, 1024x1024), {warm} warm-up; {arm.what}; "
+              f"torch CPU ops, {arm.cores} threads")
     print(json.dumps({
         "impl": "reference", "metric": METRIC, "value": v, "unit": "sketches/s", "n_gpus": args.gpus, "steps": steps,
         "warmup": warm, "ms_per_step": 1e3 * sum(ts) / steps, "higher_is_better": True, "scaling": "weak",
         "vs_baseline": None, "dtype": "f32", "data": "synthetic",
         "config": {"workload": f"SAM {MODEL} 1024x1024 sketch encode + {BOXES}-box decode + post-process", "model": MODEL},
-        "cpu_baseline": {"value": v, "unit": "sketches/s", "cores": cores, "kind": "port", "sample": sample},
+        "cpu_baseline": {"value": v, "unit": "sketches/s", "cores": arm.cores, "kind": arm.kind, "sample": sample},
         "e2e": {"value": v, "unit": "sketches/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
     }))
 
 
-# ------------------------------------------------------------------------------------------------ B200 arm
 def cpu_baseline_sample():
-    """Oracle (CPU port of the reference path) on the host cores: one ViT-H sketch with 16 boxes, timed once after
-    no warm-up (about 10-30 s of CPU work)."""
-    import torch
-
-    from inklayer_b200.config import CONFIGS
-    from inklayer_b200.weights import synthetic_state_dict
-    from oracle import sam_oracle as O
-
-    cores = os.cpu_count() or 1
-    torch.set_num_threads(cores)
-    imgs, boxes, np = synth_inputs(0, 1)
-    pred = O.OraclePredictor(O.CONFIGS[MODEL], synthetic_state_dict(CONFIGS[MODEL], 0))
-    t0 = time.perf_counter()
-    pred.set_image(imgs[0])
-    pred.predict_torch(O.apply_boxes(torch.from_numpy(boxes[0]), imgs[0].shape[:2]))
-    dt = time.perf_counter() - t0
-    return {"value": 1.0 / dt, "unit": "sketches/s", "cores": cores, "kind": "port",
-            "sample": f"1 sketch (ViT-H fp32, {BOXES} boxes) through oracle/sam_oracle.py in {dt:.1f} s, torch CPU ops, {cores} threads"}
+    """The CPU arm inside the B200 run: one warm-up, then the median of 3 timed sketches (about 20 s of CPU work)."""
+    arm = CpuArm()
+    arm.one()
+    runs = [arm.one() for _ in range(3)]
+    ts = sorted(r[0] for r in runs)
+    dt = ts[1]
+    return {"value": 1.0 / dt, "unit": "sketches/s", "cores": arm.cores, "kind": arm.kind,
+            "sample": f"1 sketch (ViT-H fp32, {BOXES} boxes, 1024x1024): median of 3 after 1 warm-up = {dt:.2f} s "
+                      f"(min {ts[0]:.2f}, max {ts[2]:.2f}); {arm.what}; torch CPU ops, {arm.cores} threads"}, runs[0][1]
 
 
-def run_b200(args):
+# ------------------------------------------------------------------------------------------------ B200 arm
+def dist_setup(args):
     import torch
     import torch.distributed as dist
-
-    from inklayer_b200 import CONFIGS, build_sam_from_state_dict
-    from inklayer_b200.pipeline import SketchSegmenter
-    from inklayer_b200.weights import synthetic_state_dict
 
     rank = int(os.environ.get("RANK", "0"))
     world = int(os.environ.get("WORLD_SIZE", "1"))
@@ -174,30 +210,29 @@ def run_b200(args):
     dev = torch.device("cuda", local)
     if world > 1:
         dist.init_process_group("nccl", device_id=dev)
+    return rank, world, local, dev
 
-    cfg = CONFIGS[MODEL]
-    sam = build_sam_from_state_dict(synthetic_state_dict(cfg, 0), cfg).to(dev)
-    imgs, boxes, np = synth_inputs(rank, BATCH)  # sketches shard by image: each rank has its own
-    seg = SketchSegmenter(sam, max_batch=BATCH)
-    d_imgs = torch.from_numpy(np.stack(imgs)).to(dev)
-    d_boxes = [torch.from_numpy(b).to(dev) for b in boxes]
-    size = (1024, 1024)
 
-    d_masks = torch.empty(BATCH * BOXES * 1024 * 1024, dtype=torch.uint8, device=dev)
-    sizes = [size] * BATCH
+def pin_to_gpu_numa_node(local: int) -> None:
+    """INKSAM_PIN_NUMA=1: keeps this rank's host threads (staging copies, hand-off) on the CPUs nvml reports as local to
+    its GPU.  Off by default: with bit-packed masks the host side moves 5 MB per sketch and is not the limiter, and on
+    boxes whose GPUs all report the same CPU set pinning only shrinks the cores a rank may use."""
+    if os.environ.get("INKSAM_PIN_NUMA") != "1":
+        return
+    try:
+        import pynvml
 
-    def step_resident():
-        feats = sam.encode(d_imgs, graph=True)  # the encoder's ~200 launches replay from a CUDA graph
-        return sam.decode_batch(feats, d_boxes, sizes, sizes, masks_out=d_masks)
+        pynvml.nvmlInit()
+        h = pynvml.nvmlDeviceGetHandleByIndex(local)
+        mask = pynvml.nvmlDeviceGetCpuAffinity(h, ((os.cpu_count() or 1) + 63) // 64)
+        cpus = {i * 64 + b for i, m in enumerate(mask) for b in range(64) if (m >> b) & 1} & os.sched_getaffinity(0)
+        if cpus:
+            os.sched_setaffinity(0, cpus)
+    except Exception:  # noqa: BLE001 -- best effort
+        pass
 
-    def step_e2e(steps=1):
-        # the public API: host uint8 sketches + host boxes in, host bool masks out; `steps` batches stream through the
-        # segmenter's copy/compute pipeline (H2D from pinned staging and D2H of every mask are inside the timed region)
-        n = 0
-        for res in seg.segment_stream((imgs, boxes) for _ in range(steps)):
-            n += len(res)
-        assert n == steps * BATCH
 
+def make_timed(torch, dist, sam, dev, world):
     def barrier():
         torch.cuda.synchronize(dev)
         if world > 1:
@@ -225,6 +260,58 @@ def run_b200(args):
             dist.all_reduce(t, op=dist.ReduceOp.MAX)
         return float(t.item()), launches, prof
 
+    return timed
+
+
+def run_b200(args):
+    import numpy as np
+    import torch
+    import torch.distributed as dist
+
+    from inklayer_b200 import CONFIGS, build_sam_from_state_dict
+    from inklayer_b200.driver import segment_shard
+    from inklayer_b200.pipeline import SketchSegmenter
+    from inklayer_b200.weights import synthetic_state_dict
+
+    rank, world, local, dev = dist_setup(args)
+    pin_to_gpu_numa_node(local)
+    cfg = CONFIGS[MODEL]
+    sam = build_sam_from_state_dict(synthetic_state_dict(cfg, 0), cfg).to(dev)
+    seg = SketchSegmenter(sam, max_batch=BATCH, packed=True)
+    timed = make_timed(torch, dist, sam, dev, world)
+
+    # sketches shard by image: rank r owns the global indices g == r (mod world) (driver.shard_indices, main.py:28 order)
+    e2e_batches = max(args.steps, E2E_MIN_BATCHES)
+    n_total = e2e_batches * BATCH * world
+    mine = list(range(rank, n_total, world))
+    imgs, boxes = synth_many(mine)
+    by_index = {g: k for k, g in enumerate(mine)}
+    d_imgs = torch.from_numpy(np.stack(imgs[:BATCH])).to(dev)
+    d_boxes = [torch.from_numpy(b).to(dev) for b in boxes[:BATCH]]
+    sizes = [(1024, 1024)] * BATCH
+    d_masks = torch.empty(BATCH * BOXES * 1024 * 128, dtype=torch.uint8, device=dev)
+
+    def step_resident():
+        feats = sam.encode(d_imgs, graph=True)  # the encoder's ~200 launches replay from a CUDA graph
+        return sam.decode_batch(feats, d_boxes, sizes, sizes, masks_out=d_masks, packed=True)
+
+    first = {}
+    loader = lambda g: imgs[by_index[g]]            # noqa: E731  (the "directory": this rank's sketches, already decoded)
+    boxes_fn = lambda g, im: boxes[by_index[g]]     # noqa: E731  (the detector's output for sketch g)
+
+    def step_e2e(paths, r, w, keep_first=False):
+        # the public API: host uint8 sketches + host boxes in, host masks out; the batches stream through the segmenter's
+        # copy / compute pipeline (H2D from pinned staging and D2H of every mask are inside the timed region)
+        got = [0]
+
+        def sink(i, masks):
+            got[0] += 1
+            if keep_first and paths[i] == 0:
+                first["packed"] = masks
+
+        segment_shard(paths, boxes_fn, seg, r, w, batch=BATCH, loader=loader, sink=sink)
+        return got[0]
+
     for _ in range(max(args.warmup, 3)):
         step_resident()
     clocks = ClockSampler(local) if rank == 0 else None
@@ -234,9 +321,14 @@ def run_b200(args):
     ms_p, _, prof = timed(step_resident, args.steps, profile=True)
     # encoder alone (config 2 of BASELINE.json: batch 8, bf16 operands) for the tensor-core utilisation figure
     ms_enc, _, _ = timed(lambda: sam.encode(d_imgs, graph=True), args.steps)
-    step_e2e(2 * (seg.depth + 1) + 1)  # every pipeline slot has captured its encoder graph before the timed region
+    feats = sam.encode(d_imgs, graph=True)
+    ms_dec, _, _ = timed(lambda: sam.decode_batch(feats, d_boxes, sizes, sizes, masks_out=d_masks, packed=True), args.steps)
+    # e2e: every pipeline slot captures its encoder graph on a few warm-up batches, then all distinct sketches stream
+    step_e2e(mine[: (2 * (seg.depth + 1) + 1) * BATCH], 0, 1)
     seg.h2d_bytes = seg.d2h_bytes = 0
-    ms_e2e, _, _ = timed(lambda: step_e2e(args.steps), 1)
+    done = []
+    ms_e2e, _, _ = timed(lambda: done.append(step_e2e(list(range(n_total)), rank, world, keep_first=(rank == 0))), 1)
+    assert done[0] == len(mine)
 
     if rank == 0:
         peak_tf, peak_gbs, peak_src = measured_peaks()
@@ -253,6 +345,18 @@ def run_b200(args):
         p_ms, p_bytes, p_n = prof["postprocess"]
         achieved = g_flop / (g_ms * 1e-3) / 1e12 if g_ms > 0 else 0.0
         enc_tf = ENC_GFLOP[MODEL] * BATCH * args.steps / (ms_enc * 1e-3) / 1e3
+        # decoder: compulsory bytes per box = 262,144 (low-res logits) + mask bits + 20; per image 2 x 2.1 MB embedding + PE
+        nbox = BATCH * BOXES
+        dec_ms = ms_dec / args.steps
+        dec_traffic = committed_traffic("decoder_traffic.json", "dram_bytes_per_pass")
+        dec_alg = nbox * (262144 + 1024 * 128 + 20) + BATCH * 2 * 256 * 4096 * 4 + 8.1e6
+        golden, gboxes = golden_masks("vit_h_bench0")
+        assert np.array_equal(gboxes, boxes[by_index[0]]), "bench sketch 0 is not the golden case vit_h_bench0"
+        e2e_masks = first["packed"].unpack()
+        ious = mask_ious(e2e_masks, golden[:, 0])
+        parity = {"min_iou": float(ious.min()), "mean_iou": float(ious.mean()), "boxes": int(len(ious)),
+                  "against": "unmodified reference (tests/golden/vit_h_bench0.npz): masks of global sketch 0 as returned by "
+                             "the timed e2e leg", "required": 0.99}
         line = {
             "metric": METRIC, "value": n_sk / (ms * 1e-3), "unit": "sketches/s", "n_gpus": world, "steps": args.steps,
             "warmup": max(args.warmup, 3), "ms_per_step": ms / args.steps, "higher_is_better": True, "scaling": "weak",
@@ -260,28 +364,176 @@ def run_b200(args):
             "config": {"workload": f"SAM {MODEL}: {BATCH} synthetic 1024x1024 sketches per step per GPU, image encoder + "
                                    f"{BOXES}-box mask decode + fused post-process per sketch; random-init weights",
                        "model": MODEL, "global_batch": BATCH * world, "boxes_per_sketch": BOXES, "parallelism": f"image-sharded x{world}, no collective",
-                       "l2": "per-step working set (1.2 GB of activations) exceeds the 126 MB L2; no flush needed"},
+                       "mask_format": "bit-packed rows, MSB first (PIL mode '1' / numpy.packbits), 131072 B per 1024x1024 mask",
+                       "l2": "per-step working set (1.2 GB of activations) exceeds the 126 MB L2; no flush needed",
+                       "e2e_stream": f"{len(mine)} distinct sketches per rank ({n_total} in all), sharded by image index"},
             "clocks": clk,
-            "e2e": {"value": n_sk / (ms_e2e * 1e-3), "unit": "sketches/s", "h2d_bytes_per_step": seg.h2d_bytes // args.steps,
-                    "d2h_bytes_per_step": seg.d2h_bytes // args.steps},
+            "e2e": {"value": n_total / (ms_e2e * 1e-3), "unit": "sketches/s",
+                    "h2d_bytes_per_step": seg.h2d_bytes // e2e_batches, "d2h_bytes_per_step": seg.d2h_bytes // e2e_batches,
+                    "sketches": n_total, "seconds": ms_e2e * 1e-3},
+            "parity": parity,
             "gpu_launches": launches,
             "roofline": {"bound": "tensor", "kernel": "gemm_tc_kernel (encoder instantiations)", "achieved": achieved, "peak": peak_tf,
-                         "unit": "TFLOP/s", "frac": achieved / peak_tf, "traffic": gemm_traffic(),
+                         "unit": "TFLOP/s", "frac": achieved / peak_tf,
+                         "traffic": committed_traffic("gemm_traffic.json", "dram_bytes_per_launch"),
                          "traffic_unit": "DRAM bytes per launch (ncu dram__bytes_read.sum + dram__bytes_write.sum, profiles/gemm_traffic.json)",
                          "algorithmic_bytes_per_launch": g_bytes / max(g_n, 1), "peak_source": peak_src + " sustained bf16",
                          "launches": g_n, "avg_launch_ms": g_ms / max(g_n, 1), "share_of_step": g_ms / ms_p},
             "encoder": {"ms_per_batch": ms_enc / args.steps, "images_per_s": BATCH * args.steps / (ms_enc * 1e-3),
                         "tflops": enc_tf, "frac_of_peak": enc_tf / peak_tf,
                         "attention_tflops": a_flop / (a_ms * 1e-3) / 1e12 if a_ms > 0 else 0.0, "attention_share_of_step": a_ms / ms_p},
-            "decoder": {"gemm_tflops": d_flop / (d_ms * 1e-3) / 1e12 if d_ms > 0 else 0.0, "gemm_share_of_step": d_ms / ms_p,
+            "decoder": {"ms_per_pass": dec_ms, "boxes_per_pass": nbox, "share_of_step": dec_ms / (ms / args.steps),
+                        "hbm_gbs": (dec_traffic / (dec_ms * 1e-3) / 1e9) if dec_traffic else None,
+                        "frac_of_hbm_peak": (dec_traffic / (dec_ms * 1e-3) / 1e9 / peak_gbs) if dec_traffic else None,
+                        "traffic": dec_traffic,
+                        "traffic_unit": "DRAM bytes of one 8 x 16-box decode pass, every kernel (ncu, profiles/decoder_traffic.json)",
+                        "compulsory_bytes_per_pass": dec_alg, "hbm_peak_gbs": peak_gbs,
+                        "gemm_tflops": d_flop / (d_ms * 1e-3) / 1e12 if d_ms > 0 else 0.0, "gemm_share_of_step": d_ms / ms_p,
                         "postprocess_gbs": p_bytes / (p_ms * 1e-3) / 1e9 if p_ms > 0 else 0.0,
                         "postprocess_frac_of_hbm_peak": (p_bytes / (p_ms * 1e-3) / 1e9) / peak_gbs if p_ms > 0 else 0.0},
         }
         if world == 1 and not args.no_cpu_baseline:
-            line["cpu_baseline"] = cpu_baseline_sample()
+            line["cpu_baseline"], cpu_masks = cpu_baseline_sample()
+            c_iou = mask_ious(e2e_masks, cpu_masks[:, 0])  # the CPU arm ran the same sketch: a second, live check
+            line["parity"]["min_iou_vs_cpu_arm"] = float(c_iou.min())
         print(json.dumps(line))
+        if parity["min_iou"] < 0.99:
+            raise SystemExit(f"parity FAILED: min IoU {parity['min_iou']:.4f} < 0.99 against the reference")
+    if world > 1:
+        dist.barrier()
+        dist.destroy_process_group()
+
+
+# ------------------------------------------------------------------------------------------------ configs 3, 4, 5
+def run_config3(args):
+    """BASELINE.json config 3: mask decoder + fused upsample / threshold over 256 boxes of one image, 1xB200."""
+    import numpy as np
+    import torch
+
+    from inklayer_b200 import CONFIGS, build_sam_from_state_dict
+    from inklayer_b200.weights import synthetic_state_dict
+
+    cfg = CONFIGS["vit_tiny"]  # the decoder is the same for every encoder size; the embedding comes from the 2-block ViT
+    sam = build_sam_from_state_dict(synthetic_state_dict(cfg, 0), cfg).to("cuda")
+    (img,), _ = synth_many([0])
+    emb = sam.encode(torch.from_numpy(img)[None].cuda())
+    rng = np.random.default_rng(2000)  # SURVEY.md 8d row 3
+    K = 256
+    x0, y0 = rng.uniform(0, 0.7 * 1024, K), rng.uniform(0, 0.7 * 1024, K)
+    w, h = rng.uniform(16, 0.3 * 1024, K), rng.uniform(16, 0.3 * 1024, K)
+    bx = torch.from_numpy(np.stack([x0, y0, np.minimum(x0 + w, 1023), np.minimum(y0 + h, 1023)], 1).astype(np.float32)).cuda()
+    peak_tf, peak_gbs, _ = measured_peaks()
+    out = {}
+    for packed in (False, True):
+        masks = torch.empty(K * 1024 * (128 if packed else 1024), dtype=torch.uint8, device="cuda")
+        run = lambda: sam.decode_batch(emb, [bx], [(1024, 1024)], [(1024, 1024)], masks_out=masks, packed=packed)  # noqa: E731
+        for _ in range(3):
+            run()
+        torch.cuda.synchronize()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        for _ in range(args.steps):
+            run()
+        e1.record(); torch.cuda.synchronize()
+        out["packed" if packed else "bytes"] = e0.elapsed_time(e1) / args.steps
+    ms = out["bytes"]
+    flop = K * 2.804e9 + 0.805e9
+    sam.profile(True)
+    masks = torch.empty(K * 1024 * 1024, dtype=torch.uint8, device="cuda")
+    sam.decode_batch(emb, [bx], [(1024, 1024)], [(1024, 1024)], masks_out=masks)
+    prof = sam.profile_read(); sam.profile(False)
+    p_ms, p_bytes, _ = prof["postprocess"]
+    print(json.dumps({"config": "3: mask decoder + fused upsample/threshold, 256 boxes of one image, 1024x1024 masks",
+                      "ms_per_image": ms, "ms_per_image_packed_masks": out["packed"], "boxes_per_s": K / ms * 1e3,
+                      "algorithmic_tflops": flop / ms / 1e9, "postprocess_ms": p_ms, "postprocess_gbs": p_bytes / p_ms / 1e6 if p_ms else None,
+                      "postprocess_frac_of_hbm_peak": (p_bytes / p_ms / 1e6) / peak_gbs if p_ms else None, "steps": args.steps}))
+
+
+def run_config4(args):
+    """BASELINE.json config 4: `main.py --dir` over N synthetic sketches (default 4096) sharded by image across the GPUs;
+    host images in, host (bit-packed) masks out through driver.segment_shard.  A bounded pool of distinct canvases per
+    rank stands for the directory (4096 x 3 MB of pixels need not sit in host memory); every sketch is still copied H2D,
+    encoded, decoded with its own boxes and copied back."""
+    import torch
+    import torch.distributed as dist
+
+    from inklayer_b200 import CONFIGS, build_sam_from_state_dict
+    from inklayer_b200.driver import segment_shard, shard_indices
+    from inklayer_b200.pipeline import SketchSegmenter
+    from inklayer_b200.synth import synthetic_boxes
+    from inklayer_b200.weights import synthetic_state_dict
+
+    rank, world, local, dev = dist_setup(args)
+    pin_to_gpu_numa_node(local)
+    cfg = CONFIGS[MODEL]
+    sam = build_sam_from_state_dict(synthetic_state_dict(cfg, 0), cfg).to(dev)
+    seg = SketchSegmenter(sam, max_batch=BATCH, packed=True)
+    n = args.sketches
+    mine = shard_indices(n, rank, world)
+    POOL = 64
+    pool_imgs, _ = synth_many(mine[:POOL])
+    loader = lambda g: pool_imgs[(g // world) % len(pool_imgs)]  # noqa: E731
+    boxes_fn = lambda g, im: synthetic_boxes(g, BOXES)  # noqa: E731
+    cnt = [0]
+
+    def sink(g, masks):
+        cnt[0] += len(masks)
+
+    segment_shard(mine[:3 * BATCH], boxes_fn, seg, 0, 1, batch=BATCH, loader=loader, sink=sink)
+    cnt[0] = 0
+    torch.cuda.synchronize(dev)
+    if world > 1:
+        dist.barrier()
+    t0 = time.perf_counter()
+    segment_shard(list(range(n)), boxes_fn, seg, rank, world, batch=BATCH, loader=loader, sink=sink)
+    torch.cuda.synchronize(dev)
+    dt = torch.tensor([time.perf_counter() - t0], dtype=torch.float64, device=dev)
+    c = torch.tensor([cnt[0]], dtype=torch.float64, device=dev)
+    if world > 1:
+        dist.all_reduce(dt, op=dist.ReduceOp.MAX)
+        dist.all_reduce(c, op=dist.ReduceOp.SUM)
+    if rank == 0:
+        print(json.dumps({"config": "4: --dir over synthetic sketches sharded by image", "model": MODEL, "sketches": n, "n_gpus": world,
+                          "boxes_per_sketch": BOXES, "masks": int(c.item()), "seconds": float(dt.item()),
+                          "sketches_per_s": n / float(dt.item()), "mask_format": "bit-packed", "host_cores": os.cpu_count()}))
     if world > 1:
         dist.destroy_process_group()
+
+
+def run_config5(args):
+    """BASELINE.json config 5: SAM ViT-B / ViT-L / ViT-H image encoder alone at batch 1, 8 and 32 (tile-shape coverage:
+    head_dim 64 and 80, D = 768 / 1024 / 1280), bf16 operands; batch 1 also through a CUDA graph (the set_image pattern)."""
+    import numpy as np
+    import torch
+
+    from inklayer_b200 import CONFIGS, build_sam_from_state_dict
+    from inklayer_b200.weights import synthetic_state_dict
+
+    peak_tf, _, _ = measured_peaks()
+    imgs8, _ = synth_many(list(range(8)))
+    rows = []
+    for name in (args.models or ["vit_b", "vit_l", "vit_h"]):
+        cfg = CONFIGS[name]
+        sam = build_sam_from_state_dict(synthetic_state_dict(cfg, 0), cfg).to("cuda")
+        sam.reserve(32, 0)
+        for B, graph in ((1, False), (1, True), (8, True), (32, True)):
+            imgs = torch.from_numpy(np.stack([imgs8[i % 8] for i in range(B)])).cuda()
+            for _ in range(3):
+                sam.encode(imgs, graph=graph)
+            torch.cuda.synchronize()
+            n = 20 if B == 1 else 5
+            e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            e0.record()
+            for _ in range(n):
+                sam.encode(imgs, graph=graph)
+            e1.record(); torch.cuda.synchronize()
+            ms = e0.elapsed_time(e1) / n
+            tf = ENC_GFLOP[name] * B / ms
+            rows.append({"model": name, "batch": B, "cuda_graph": graph, "ms_per_batch": round(ms, 3), "images_per_s": round(B / ms * 1e3, 1),
+                         "tflops": round(tf, 1), "frac_of_sustained_peak": round(tf / peak_tf, 3)})
+        del sam
+        torch.cuda.empty_cache()
+    print(json.dumps({"config": "5: encoder width/depth sweep", "peak_tflops": peak_tf, "rows": rows}))
 
 
 def main():
@@ -290,10 +542,19 @@ def main():
     ap.add_argument("--steps", type=int, default=10)
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
-    ap.add_argument("--no-cpu-baseline", action="store_true", help="skip the ~20 s oracle timing (profiling runs)")
+    ap.add_argument("--config", type=int, default=0, choices=[0, 3, 4, 5], help="another BASELINE.json configuration")
+    ap.add_argument("--sketches", type=int, default=4096, help="--config 4: sketches in the synthetic directory")
+    ap.add_argument("--models", nargs="*", help="--config 5: subset of vit_b vit_l vit_h")
+    ap.add_argument("--no-cpu-baseline", action="store_true", help="skip the ~20 s CPU arm (profiling runs)")
     args = ap.parse_args()
     if args.impl == "reference":
         run_reference(args)
+    elif args.config == 3:
+        run_config3(args)
+    elif args.config == 4:
+        run_config4(args)
+    elif args.config == 5:
+        run_config5(args)
     else:
         run_b200(args)
 

@@ -88,6 +88,13 @@ int inksam_decode_batch(inksam_handle* h, const float* embeddings, int B, const 
                         const int* in_hw, const int* orig_hw, uint8_t* masks_out, float* iou_out, float* lowres_out,
                         float* logits_out, float mask_threshold, void* stream);
 
+/* inksam_decode_batch with BIT-PACKED masks: mask_bits_out holds, image after image, counts[i] maps of
+ * orig_h x ceil(orig_w / 8) bytes (leftmost pixel in the MSB, rows padded to whole bytes with zero bits: numpy.packbits
+ * / PIL mode "1" rows, what InkLayer/runner.py:51 turns the masks into).  8x less device->host traffic than byte masks. */
+int inksam_decode_batch_packed(inksam_handle* h, const float* embeddings, int B, const float* boxes, const int* counts,
+                               const int* in_hw, const int* orig_hw, uint8_t* mask_bits_out, float* iou_out,
+                               float* lowres_out, float mask_threshold, void* stream);
+
 /* Workspace.  The library owns its workspace.  inksam_workspace_bytes: what encodes of up to max_batch
  * images per call and decodes of up to max_batch images with up to max_boxes boxes in total need.  inksam_reserve sizes
  * the workspace once for that envelope (synchronises the device; releases buffers retired by earlier growth) so that no

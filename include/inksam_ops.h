@@ -79,6 +79,10 @@ int inksam_op_fill_pad_rows(void* qkv, const float* bias, int B, int cols, void*
 /* Sam.postprocess_masks + threshold, fused. modeling/sam.py:133-162, predictor.py:238-241. */
 int inksam_op_postprocess(const float* low, unsigned char* masks, float* logits, int K, int in_h, int in_w, int H, int W,
                           float thr, void* stream);
+/* The same with bit-packed masks: mask_bits is uint8 [K][H][(W+7)/8], leftmost pixel in the MSB, rows padded to whole
+ * bytes with zero bits -- numpy.packbits(axis=-1) / PIL mode "1" rows, the format InkLayer/runner.py:51 converts to. */
+int inksam_op_postprocess_packed(const float* low, unsigned char* mask_bits, int K, int in_h, int in_w, int H, int W, float thr,
+                                 void* stream);
 
 /* ResizeLongestSide.apply_image on the device: Pillow's 8-bit bilinear resample (torchvision resize of a PIL image,
  * SA/utils/transforms.py:26-31; algorithm of Pillow libImaging/Resample.c), bit-exact with the host path.

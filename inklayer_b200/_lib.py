@@ -33,6 +33,8 @@ SIGNATURES = {
                                     c_void_p, c_void_p, c_float, c_void_p]),
     "inksam_decode_batch": (c_int, [c_void_p, c_void_p, c_int, c_void_p, POINTER(c_int), POINTER(c_int), POINTER(c_int),
                                     c_void_p, c_void_p, c_void_p, c_void_p, c_float, c_void_p]),
+    "inksam_decode_batch_packed": (c_int, [c_void_p, c_void_p, c_int, c_void_p, POINTER(c_int), POINTER(c_int), POINTER(c_int),
+                                           c_void_p, c_void_p, c_void_p, c_float, c_void_p]),
     "inksam_workspace_bytes": (c_size_t, [c_void_p, c_int, c_int]),
     "inksam_reserve": (c_int, [c_void_p, c_int, c_int]),
     "inksam_workspace_generation": (c_longlong, [c_void_p]),
@@ -57,6 +59,7 @@ SIGNATURES = {
                                    POINTER(c_float), POINTER(c_float), c_void_p, c_void_p]),
     "inksam_op_fill_pad_rows": (c_int, [c_void_p, c_void_p, c_int, c_int, c_void_p]),
     "inksam_op_postprocess": (c_int, [c_void_p, c_void_p, c_void_p, c_int, c_int, c_int, c_int, c_int, c_float, c_void_p]),
+    "inksam_op_postprocess_packed": (c_int, [c_void_p, c_void_p, c_int, c_int, c_int, c_int, c_int, c_float, c_void_p]),
     "inksam_resize_workspace_bytes": (c_size_t, [c_int, c_int, c_int, c_int]),
     "inksam_resize_u8": (c_int, [c_void_p, c_int, c_int, c_longlong, c_void_p, c_int, c_int, c_longlong, c_void_p, c_void_p]),
 }

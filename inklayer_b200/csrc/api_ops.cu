@@ -80,4 +80,9 @@ int inksam_op_postprocess(const float* low, unsigned char* masks, float* logits,
   return launch_postprocess(low, masks, logits, K, in_h, in_w, H, W, thr, static_cast<cudaStream_t>(stream));
 }
 
+int inksam_op_postprocess_packed(const float* low, unsigned char* mask_bits, int K, int in_h, int in_w, int H, int W, float thr,
+                                 void* stream) {
+  return launch_postprocess(low, mask_bits, nullptr, K, in_h, in_w, H, W, thr, static_cast<cudaStream_t>(stream), 1);
+}
+
 }  // extern "C"

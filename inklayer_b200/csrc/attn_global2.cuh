@@ -13,8 +13,10 @@
 // P(t) (bf16) is written back over the first 32 columns of S(t).  The prologue borrows all 512 columns for the
 // rel-pos products T_h / T_w of both tiles (T[q][r] = q . rel_pos[r] on the UNSCALED q, image_encoder.py:234,354-355)
 // and the K ring for the tables.
-// Softmax follows attn_tc.cuh: exp2 with a fixed shift taken from the first 32 keys, exact power-of-two rescale once
-// the running sum passes 2^32 (cold path).
+// Softmax: exp2 with a shift taken from the first 32 keys and no per-element maximum in the hot loop; two cold paths keep
+// it exact for any logit range: a sub-tile whose sum reaches 2^100 (a key that may have hit the 2^120 exponent clamp) is
+// redone with the shift raised to its true maximum BEFORE its P is used, and once the running sum passes 2^32 the shift
+// moves up by floor(log2 l) -- both are exact power-of-two rescales of l and O.
 #pragma once
 #include "attn_tc.cuh"
 
@@ -280,12 +282,64 @@ attn_global2_kernel(const __grid_constant__ CUtensorMap tm64, const __grid_const
         l2 = f2_add(l2, f2_pack(p0, p1));
         pk[16 + (i >> 1)] = pack_bf16x2(p0, p1);
       }
+      float lsub;
       {
         float la, lb;
         f2_unpack(l2, la, lb);
-        l += la + lb;
+        lsub = la + lb;
         l2 = f2_pack(0.f, 0.f);
       }
+      // The exponent is clamped at 120 above so that a key far above the shift cannot produce inf.  A sub-tile whose sum
+      // reaches 2^100 holds a key more than 94 log2 units above the shift, i.e. possibly a CLAMPED one: before P(t) is
+      // handed to the tensor cores the shift is raised to this sub-tile's true maximum, everything accumulated so far is
+      // rescaled by the exact power of two, and the sub-tile is exponentiated again.  Exact for any logit range; cold.
+      if (__any_sync(0xffffffffu, lsub > 1.2676506e30f)) {
+        const bool hot = lsub > 1.2676506e30f;
+        float mx = -INFINITY;
+#pragma unroll
+        for (int i = 0; i < 32; i += 2) {
+          float b0, b1, d0, d1;
+          f2_unpack(bW2[i >> 1], b0, b1);
+          f2_unpack(bW2[16 + (i >> 1)], d0, d1);
+          mx = fmaxf(mx, fmaxf(fmaf(__uint_as_float(v0[i]), c1, b0), fmaf(__uint_as_float(v0[i + 1]), c1, b1)));
+          mx = fmaxf(mx, fmaxf(fmaf(__uint_as_float(v1[i]), c1, d0), fmaf(__uint_as_float(v1[i + 1]), c1, d1)));
+        }
+        const float delta = hot ? ceilf(mx + bb) : 0.f;  // integer, > 94: an exact power-of-two rescale
+        const float alpha = hot ? ex2_approx(-delta) : 1.f;  // flushes to 0 when the old terms no longer matter
+        if (t > 0) {
+          mbar_wait(bar_pvdone(g, buf ^ 1), (uint32_t)(((t - 1) >> 1) & 1));  // PV(t-1): O holds every earlier sub-tile
+          tc_fence_after();
+          uint32_t v[16];
+#pragma unroll
+          for (int c = 0; c < HD / 16; ++c) {
+            tmem_ld_32x16(o_addr + c * 16, v);
+            tmem_ld_wait();
+#pragma unroll
+            for (int i = 0; i < 16; ++i) v[i] = __float_as_uint(__uint_as_float(v[i]) * alpha);
+            tmem_st_32x16(o_addr + c * 16, v);
+          }
+          tmem_st_wait();
+          tc_fence_before();
+        }
+        m_used += delta;
+        l *= alpha;
+        const float bn = bb - delta;
+        lsub = 0.f;
+#pragma unroll
+        for (int i = 0; i < 32; i += 2) {
+          float b0, b1, d0, d1;
+          f2_unpack(bW2[i >> 1], b0, b1);
+          f2_unpack(bW2[16 + (i >> 1)], d0, d1);
+          const float p0 = ex2_approx(fmaf(__uint_as_float(v0[i]), c1, b0 + bn));
+          const float p1 = ex2_approx(fmaf(__uint_as_float(v0[i + 1]), c1, b1 + bn));
+          const float p2 = ex2_approx(fmaf(__uint_as_float(v1[i]), c1, d0 + bn));
+          const float p3 = ex2_approx(fmaf(__uint_as_float(v1[i + 1]), c1, d1 + bn));
+          lsub += (p0 + p1) + (p2 + p3);
+          pk[i >> 1] = pack_bf16x2(p0, p1);
+          pk[16 + (i >> 1)] = pack_bf16x2(p2, p3);
+        }
+      }
+      l += lsub;
       tmem_st_32x32(s_addr, pk);  // P(t) over the first 32 columns of S(t), all of which have been read
       tmem_st_wait();
       tc_fence_before();

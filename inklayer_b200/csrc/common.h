@@ -61,10 +61,11 @@ int launch_fold_ln_weights(const float* W, const float* gamma, const float* beta
 int launch_fill_pad_rows(void* qkv, const float* bias, int B, int cols, cudaStream_t st);
 int launch_repack(const float* in, void* out, int out_bf16, const long long* ishape, int ndim, const int* perm,
                   cudaStream_t st);
+// packed: masks are 1 bit per pixel, MSB first, rows padded to whole bytes ([K][H][(W+7)/8]) instead of one byte per pixel
 int launch_postprocess(const float* low, unsigned char* masks, float* logits, int K, int in_h, int in_w, int H, int W,
-                       float thr, cudaStream_t st);
+                       float thr, cudaStream_t st, int packed = 0);
 // boxes of several images (segments with their own geometry) in one launch; in_hw / orig_hw: [nseg][2]
 int launch_postprocess_batch(int nseg, const float* const* low, unsigned char* const* masks, float* const* logits, const int* n,
-                             const int* in_hw, const int* orig_hw, float thr, cudaStream_t st);
+                             const int* in_hw, const int* orig_hw, float thr, cudaStream_t st, int packed = 0);
 
 }  // namespace inksam

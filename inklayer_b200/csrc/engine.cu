@@ -574,13 +574,14 @@ DecLayout dec_layout(int B, int K) {
 }
 
 // Per-image geometry of a decode batch (host side).
-struct ImgGeom { int in_h, in_w, H, W; size_t mask_off; };  // mask_off: element offset of the image's first mask
+// mask_off: element offset of the image's first map (logits); mask_byte_off: byte offset of its first mask (byte or packed)
+struct ImgGeom { int in_h, in_w, H, W; size_t mask_off, mask_byte_off; };
 
 // One pass over boxes [k0, k0+n) of the batch.  keys0 / kvq0: per-image layer-0 keys and their merged k|v|q projection;
 // box_img: device array, image index of every box of the batch.
 int decode_chunk(inksam_handle* h, const float* keys0, const float* kvq0, char* ws, const float* boxes, const int* box_img,
                  int k0, int n, const BoxSegments& seg, const std::vector<ImgGeom>& geom, uint8_t* masks, float* iou,
-                 float* low, float* logits, float thr, cudaStream_t st) {
+                 float* low, float* logits, float thr, bool packed, cudaStream_t st) {
   const std::string T = "mask_decoder.transformer.layers.";
   // per-chunk buffers
   size_t off = 0;
@@ -685,19 +686,21 @@ int decode_chunk(inksam_handle* h, const float* keys0, const float* kvq0, char* 
       if (b1 <= b0) continue;
       const ImgGeom& gm = geom[i];
       const size_t HW = (size_t)gm.H * gm.W;
+      const size_t mbytes = packed ? (size_t)gm.H * ((gm.W + 7) / 8) : HW;  // bytes of one mask
       const size_t mo = gm.mask_off + (size_t)(b0 - seg.start[i]) * HW;
       p_low[ns] = low + (size_t)(b0 - k0) * 65536;
-      p_mask[ns] = masks ? masks + mo : nullptr;
+      p_mask[ns] = masks ? masks + gm.mask_byte_off + (size_t)(b0 - seg.start[i]) * mbytes : nullptr;
       p_log[ns] = logits ? logits + mo : nullptr;
       cnt[ns] = b1 - b0;
       in_hw[2 * ns] = gm.in_h; in_hw[2 * ns + 1] = gm.in_w; orig_hw[2 * ns] = gm.H; orig_hw[2 * ns + 1] = gm.W;
-      bytes += (double)(b1 - b0) * (65536.0 * 4 + (double)HW * ((masks ? 1 : 0) + (logits ? 4 : 0)));
+      bytes += (double)(b1 - b0) * (65536.0 * 4 + (masks ? (double)mbytes : 0.0) + (logits ? 4.0 * (double)HW : 0.0));
       ++ns;
     }
     if (ns > 0 && (masks || logits)) {
       ++h->launches;
       Prof p(h, CAT_POST, bytes, st);
-      INK_TRY(launch_postprocess_batch(ns, p_low, masks ? p_mask : nullptr, logits ? p_log : nullptr, cnt, in_hw, orig_hw, thr, st));
+      INK_TRY(launch_postprocess_batch(ns, p_low, masks ? p_mask : nullptr, logits ? p_log : nullptr, cnt, in_hw, orig_hw, thr, st,
+                                       packed ? 1 : 0));
     }
   }
   return 0;
@@ -705,9 +708,10 @@ int decode_chunk(inksam_handle* h, const float* keys0, const float* kvq0, char* 
 
 }  // namespace
 
-extern "C" int inksam_decode_batch(inksam_handle* h, const float* embeddings, int B, const float* boxes, const int* counts,
-                                   const int* in_hw, const int* orig_hw, uint8_t* masks_out, float* iou_out,
-                                   float* lowres_out, float* logits_out, float mask_threshold, void* stream) {
+namespace {
+int decode_batch_impl(inksam_handle* h, const float* embeddings, int B, const float* boxes, const int* counts,
+                      const int* in_hw, const int* orig_hw, uint8_t* masks_out, float* iou_out, float* lowres_out,
+                      float* logits_out, float mask_threshold, bool packed, void* stream) {
   if (!h || !embeddings || !counts || !in_hw || !orig_hw || !iou_out || !lowres_out)
     return set_error("inksam_decode_batch: null argument");
   if (!h->finalized) return set_error("inksam_decode_batch: weights not finalized (call inksam_finalize_weights)");
@@ -715,7 +719,7 @@ extern "C" int inksam_decode_batch(inksam_handle* h, const float* embeddings, in
   BoxSegments seg{};
   seg.n = B;
   std::vector<ImgGeom> geom(B);
-  size_t moff = 0;
+  size_t moff = 0, mboff = 0;
   for (int i = 0; i < B; ++i) {
     if (counts[i] < 0) return set_error("inksam_decode_batch: counts[%d]=%d", i, counts[i]);
     seg.start[i + 1] = seg.start[i] + counts[i];
@@ -724,7 +728,9 @@ extern "C" int inksam_decode_batch(inksam_handle* h, const float* embeddings, in
     if (gm.in_h < 1 || gm.in_w < 1 || gm.in_h > 1024 || gm.in_w > 1024 || gm.H < 1 || gm.W < 1)
       return set_error("inksam_decode_batch: image %d: bad sizes input %dx%d original %dx%d", i, gm.in_h, gm.in_w, gm.H, gm.W);
     gm.mask_off = moff;
+    gm.mask_byte_off = mboff;
     moff += (size_t)counts[i] * gm.H * gm.W;
+    mboff += (size_t)counts[i] * gm.H * (packed ? (size_t)((gm.W + 7) / 8) : (size_t)gm.W);
   }
   const int K = seg.start[B];
   if (K == 0) return 0;
@@ -755,9 +761,24 @@ extern "C" int inksam_decode_batch(inksam_handle* h, const float* embeddings, in
   for (int k0 = 0; k0 < K; k0 += kBoxChunk) {
     const int n = K - k0 < kBoxChunk ? K - k0 : kBoxChunk;
     INK_TRY(decode_chunk(h, keys0, kvq0, ws + shared_bytes, boxes, box_img, k0, n, seg, geom, masks_out, iou_out, lowres_out,
-                         logits_out, mask_threshold, st));
+                         logits_out, mask_threshold, packed, st));
   }
   return 0;
+}
+}  // namespace
+
+extern "C" int inksam_decode_batch(inksam_handle* h, const float* embeddings, int B, const float* boxes, const int* counts,
+                                   const int* in_hw, const int* orig_hw, uint8_t* masks_out, float* iou_out,
+                                   float* lowres_out, float* logits_out, float mask_threshold, void* stream) {
+  return decode_batch_impl(h, embeddings, B, boxes, counts, in_hw, orig_hw, masks_out, iou_out, lowres_out, logits_out,
+                           mask_threshold, false, stream);
+}
+
+extern "C" int inksam_decode_batch_packed(inksam_handle* h, const float* embeddings, int B, const float* boxes, const int* counts,
+                                          const int* in_hw, const int* orig_hw, uint8_t* mask_bits_out, float* iou_out,
+                                          float* lowres_out, float mask_threshold, void* stream) {
+  return decode_batch_impl(h, embeddings, B, boxes, counts, in_hw, orig_hw, mask_bits_out, iou_out, lowres_out, nullptr,
+                           mask_threshold, true, stream);
 }
 
 extern "C" int inksam_decode_boxes(inksam_handle* h, const float* embedding, const float* boxes, int K, int in_h, int in_w,

@@ -13,7 +13,7 @@
 //   general: per-column tap tables (outer tap + its two inner taps) are built once per tile in shared memory; a warp
 //            produces 128 consecutive pixels of one row per pass (mask bytes assembled from ballots, one 4-byte store
 //            per lane); the two virtual rows share their low-res rows whenever they fall between the same pair.
-// Algorithmic bytes per box: 262,144 read + H*W written.
+// Algorithmic bytes per box: 262,144 read + H*W written; H*ceil(W/8) written in the bit-packed format.
 #include "common.h"
 #include "decoder_ops.h"
 
@@ -35,9 +35,11 @@ __device__ __forceinline__ Tap src_tap(int dst, float scale, int in_size) {
 
 struct PostSeg {
   const float* low;      // [nbox][256][256]
-  unsigned char* masks;  // [nbox][H][W] or null
+  unsigned char* masks;  // [nbox][H][W] bytes 0/1, or (packed) [nbox][H][(W+7)/8] bits, or null
   float* logits;         // [nbox][H][W] or null
   int in_h, in_w, H, W;
+  int packed, pitch;     // packed: 1 bit per pixel, leftmost pixel in the MSB, rows padded to whole bytes (numpy packbits /
+                         // PIL mode "1" row layout, what InkLayer/runner.py:51 converts the masks to); pitch = bytes per row
   int nbox, tile0;       // tile0: index of the segment's first tile in the grid
   float sy, sx;
 };
@@ -55,7 +57,7 @@ __device__ __forceinline__ void post_fast(const PostSeg& sg, int box, int band, 
   const int W = sg.W, H = sg.H;
   const int segs = W >> 4;                   // 16-pixel segments per row
   const float* lo = sg.low + (size_t)box * 65536;
-  unsigned char* out = sg.masks + (size_t)box * H * W;
+  unsigned char* out = sg.masks + (size_t)box * H * (sg.packed ? sg.pitch : W);
   // the tile is 16 rows: four 4-row groups; threads sweep (group, segment)
   for (int it = threadIdx.x; it < (kRows / 4) * segs; it += blockDim.x) {
     const int grp = it / segs, s = it - grp * segs;
@@ -107,7 +109,17 @@ __device__ __forceinline__ void post_fast(const PostSeg& sg, int box, int band, 
         }
         w[q] = word;
       }
-      *reinterpret_cast<uint4*>(out + (size_t)y * W + 16 * s) = make_uint4(w[0], w[1], w[2], w[3]);
+      if (sg.packed) {  // 16 pixels -> 2 bytes, pixel 0 in bit 7 of the first byte
+        unsigned int bits = 0;
+#pragma unroll
+        for (int q = 0; q < 4; ++q) {
+          const unsigned int nib = (w[q] & 1u) << 3 | ((w[q] >> 8) & 1u) << 2 | ((w[q] >> 16) & 1u) << 1 | ((w[q] >> 24) & 1u);
+          bits = (bits << 4) | nib;
+        }
+        *reinterpret_cast<unsigned short*>(out + (size_t)y * sg.pitch + 2 * s) = (unsigned short)((bits >> 8) | ((bits & 0xffu) << 8));
+      } else {
+        *reinterpret_cast<uint4*>(out + (size_t)y * W + 16 * s) = make_uint4(w[0], w[1], w[2], w[3]);
+      }
     }
   }
 }
@@ -137,7 +149,7 @@ __device__ __forceinline__ void post_general(const PostSeg& sg, int box, int ban
       const int r = it / groups, g = it - r * groups;
       const int y = y_begin + r;
       const size_t rowo = obase + (size_t)y * W + xc;
-      const int mis = sg.masks ? (int)((reinterpret_cast<uintptr_t>(sg.masks) + rowo) & 3) : 0;
+      const int mis = (sg.masks && !sg.packed) ? (int)((reinterpret_cast<uintptr_t>(sg.masks) + rowo) & 3) : 0;
       const int xs = 128 * g - mis;  // chunk-relative column of the group's first pixel (negative in the head group)
       if (xs >= cw) continue;
       const Tap ty = src_tap(y, sg.sy, in_h);
@@ -172,7 +184,25 @@ __device__ __forceinline__ void post_general(const PostSeg& sg, int box, int ban
         }
         bal[e] = __ballot_sync(0xffffffffu, ok && v > thr);
       }
-      if (sg.masks) {
+      if (sg.masks && sg.packed) {
+        // ballot e holds pixels xs + 32e .. +31 (bit = lane): reversed and byte-swapped it is the 4 packed bytes of those
+        // pixels in memory order; lane e < 4 stores them (pixels beyond the row voted 0: the padding bits are zero)
+        if (lane < 4) {
+          const int px = xs + 32 * lane;  // xs = 128 g here (mis == 0)
+          if (px < cw) {
+            const unsigned int word = __byte_perm(__brev(bal[lane]), 0, 0x0123);
+            unsigned char* o = sg.masks + ((size_t)box * H + y) * sg.pitch + ((xc + px) >> 3);
+            const int nb = (cw - px + 7) >> 3;  // bytes of this row that remain from px on
+            if (nb >= 4 && (reinterpret_cast<uintptr_t>(o) & 3) == 0) {
+              *reinterpret_cast<unsigned int*>(o) = word;
+            } else {
+#pragma unroll
+              for (int e = 0; e < 4; ++e)
+                if (e < nb) o[e] = (unsigned char)((word >> (8 * e)) & 0xffu);
+            }
+          }
+        }
+      } else if (sg.masks) {
         // lane l owns pixels xs + 4l .. xs + 4l + 3: bits (4l & 31) .. +3 of ballot word l / 8
         const unsigned int src = (lane < 8) ? bal[0] : (lane < 16) ? bal[1] : (lane < 24) ? bal[2] : bal[3];
         const unsigned int bits = (src >> ((4 * lane) & 31)) & 0xfu;
@@ -203,17 +233,18 @@ __global__ void __launch_bounds__(256) postprocess_kernel(const __grid_constant_
   const int t = blockIdx.x - sg.tile0;
   const int box = t / bands, band = t - box * bands;
   const bool fast = sg.in_h == sg.H && sg.in_w == sg.W && (sg.W & 15) == 0 && sg.logits == nullptr && sg.masks != nullptr &&
-                    (reinterpret_cast<uintptr_t>(sg.masks) & 15) == 0;
+                    (reinterpret_cast<uintptr_t>(sg.masks) & 15) == 0;  // (packed rows of W % 16 == 0 pixels are 2-byte aligned)
   if (fast) post_fast(sg, box, band, thr);
   else post_general(sg, box, band, thr, tab_i, tab_l);
 }
 
 static int add_segment(PostBatch& pb, int& tiles, const float* low, unsigned char* masks, float* logits, int K, int in_h,
-                       int in_w, int H, int W) {
+                       int in_w, int H, int W, int packed) {
   if (in_h < 1 || in_w < 1 || in_h > 1024 || in_w > 1024 || H < 1 || W < 1)
     return set_error("postprocess: bad sizes input %dx%d original %dx%d", in_h, in_w, H, W);
   PostSeg& s = pb.s[pb.nseg++];
   s.low = low; s.masks = masks; s.logits = logits; s.in_h = in_h; s.in_w = in_w; s.H = H; s.W = W; s.nbox = K;
+  s.packed = packed ? 1 : 0; s.pitch = (W + 7) / 8;
   s.sy = (float)in_h / (float)H; s.sx = (float)in_w / (float)W;
   s.tile0 = tiles;
   tiles += K * ((H + kRows - 1) / kRows);
@@ -222,11 +253,11 @@ static int add_segment(PostBatch& pb, int& tiles, const float* low, unsigned cha
 
 // low: [K][256][256] fp32; masks: [K][H][W] uint8 (0/1) or null; logits: [K][H][W] fp32 or null.
 int launch_postprocess(const float* low, unsigned char* masks, float* logits, int K, int in_h, int in_w, int H, int W,
-                       float thr, cudaStream_t st) {
+                       float thr, cudaStream_t st, int packed) {
   if (K <= 0) return 0;
   PostBatch pb{};
   int tiles = 0;
-  INK_TRY(add_segment(pb, tiles, low, masks, logits, K, in_h, in_w, H, W));
+  INK_TRY(add_segment(pb, tiles, low, masks, logits, K, in_h, in_w, H, W, packed));
   postprocess_kernel<<<tiles, 256, 0, st>>>(pb, thr);
   CUDA_TRY(cudaGetLastError());
   return 0;
@@ -234,14 +265,14 @@ int launch_postprocess(const float* low, unsigned char* masks, float* logits, in
 
 // Several images' boxes in one launch: segment i has n[i] boxes whose logits start at low[i], output at masks[i] / logits[i].
 int launch_postprocess_batch(int nseg, const float* const* low, unsigned char* const* masks, float* const* logits, const int* n,
-                             const int* in_hw, const int* orig_hw, float thr, cudaStream_t st) {
+                             const int* in_hw, const int* orig_hw, float thr, cudaStream_t st, int packed) {
   if (nseg > kMaxDecodeImages) return set_error("postprocess: %d segments > %d", nseg, kMaxDecodeImages);
   PostBatch pb{};
   int tiles = 0;
   for (int i = 0; i < nseg; ++i) {
     if (n[i] <= 0) continue;
     INK_TRY(add_segment(pb, tiles, low[i], masks ? masks[i] : nullptr, logits ? logits[i] : nullptr, n[i], in_hw[2 * i],
-                        in_hw[2 * i + 1], orig_hw[2 * i], orig_hw[2 * i + 1]));
+                        in_hw[2 * i + 1], orig_hw[2 * i], orig_hw[2 * i + 1], packed));
   }
   if (tiles == 0) return 0;
   postprocess_kernel<<<tiles, 256, 0, st>>>(pb, thr);

@@ -52,9 +52,13 @@ def batched(items: Sequence, size: int) -> Iterator[Sequence]:
 
 
 def segment_shard(paths: Sequence[str], boxes_fn: BoxesFn, segmenter, rank: int = 0, world: int = 1,
-                  batch: Optional[int] = None, loader: Callable[[str], np.ndarray] = load_sketch) -> Dict[int, List[np.ndarray]]:
+                  batch: Optional[int] = None, loader: Callable[[str], np.ndarray] = load_sketch,
+                  sink: Optional[Callable[[int, object], None]] = None) -> Dict[int, List[np.ndarray]]:
     """Runs this rank's shard of `paths` through `segmenter.segment_stream`; returns {global image index: list of K bool
-    masks [H,W]} in the form `run_SAM` returns them (a list per image; empty list for an image without boxes)."""
+    masks [H,W]} in the form `run_SAM` returns them (a list per image; empty list for an image without boxes).
+    With `sink`, every image's result (bool arrays, or PackedMasks from a packed segmenter) is handed to
+    sink(global index, masks) as soon as its batch completes and nothing is accumulated (a 4096-sketch directory is
+    64 GB of byte masks)."""
     mine = shard_indices(len(paths), rank, world)
     batch = batch or getattr(segmenter, "max_batch", 1)
     groups = list(batched(mine, batch))
@@ -67,7 +71,10 @@ def segment_shard(paths: Sequence[str], boxes_fn: BoxesFn, segmenter, rank: int 
     out: Dict[int, List[np.ndarray]] = {}
     for g, res in zip(groups, segmenter.segment_stream(feed())):
         for i, masks in zip(g, res):
-            out[i] = [m for m in masks]
+            if sink is not None:
+                sink(i, masks)
+            else:
+                out[i] = [m for m in (masks.unpack() if hasattr(masks, "unpack") else masks)]
     return out
 
 
@@ -103,7 +110,7 @@ def gather_results(local: Dict[int, List[np.ndarray]], n: int, rank: int = 0, wo
     return [dec(merged[i]) for i in range(n)]
 
 
-def write_masks(out_base_dir: str, path: str, masks: Sequence[np.ndarray]) -> str:
+def write_masks(out_base_dir: str, path: str, masks) -> str:
     """The hand-off format to the refinement stage: `<out>/<name>/masks/mask_{i}.png`, PIL mode "1"
     (runner.py:22,51,55-60)."""
     from PIL import Image
@@ -111,6 +118,10 @@ def write_masks(out_base_dir: str, path: str, masks: Sequence[np.ndarray]) -> st
     name = os.path.basename(path).split(".")[0]
     masks_dir = os.path.join(out_base_dir, name, "masks")
     os.makedirs(masks_dir, exist_ok=True)
+    if hasattr(masks, "to_pil"):  # PackedMasks: the mode "1" image is built from the packed rows directly
+        for i in range(len(masks)):
+            masks.to_pil(i).save(os.path.join(masks_dir, f"mask_{i}.png"))
+        return masks_dir
     for i, m in enumerate(masks):
         Image.fromarray(np.asarray(m, dtype=bool)).save(os.path.join(masks_dir, f"mask_{i}.png"))
     return masks_dir
@@ -118,7 +129,9 @@ def write_masks(out_base_dir: str, path: str, masks: Sequence[np.ndarray]) -> st
 
 def run_directory(directory: str, out_dir: str, boxes_fn: BoxesFn, segmenter=None, write: bool = True):
     """`main.py --dir DIR --out_dir OUT` for the SAM stage under torchrun (or a single process).  Reads RANK / WORLD_SIZE
-    from the environment; builds the B200 segmenter on this rank's GPU when none is given."""
+    from the environment; builds the B200 segmenter on this rank's GPU when none is given (checkpoint path from
+    $INKSAM_CHECKPOINT, else the reference's default models/sam_vit_h_4b8939.pth; a missing file raises).
+    Returns (paths, {global index: masks directory}) when writing, else (paths, {global index: list of bool masks})."""
     rank, world = int(os.environ.get("RANK", "0")), int(os.environ.get("WORLD_SIZE", "1"))
     paths = list_sketches(directory)
     if segmenter is None:
@@ -131,8 +144,12 @@ def run_directory(directory: str, out_dir: str, boxes_fn: BoxesFn, segmenter=Non
         # a missing checkpoint raises (InkLayer/segmentor/sam.py:17-19 stops there too); never synthetic weights
         segmenter = segmenter_for_checkpoint(os.environ.get("INKSAM_CHECKPOINT", default_ckpt), torch.device("cuda", local),
                                              max_batch=8)
-    local_res = segment_shard(paths, boxes_fn, segmenter, rank, world)
-    if write:
-        for i, masks in local_res.items():
-            write_masks(out_dir, paths[i], masks)
-    return paths, local_res
+    if not write:
+        return paths, segment_shard(paths, boxes_fn, segmenter, rank, world)
+    written: Dict[int, str] = {}  # masks go to disk as their batch completes; nothing is accumulated in host memory
+
+    def sink(i: int, masks) -> None:
+        written[i] = write_masks(out_dir, paths[i], masks)
+
+    segment_shard(paths, boxes_fn, segmenter, rank, world, sink=sink)
+    return paths, written

@@ -44,6 +44,32 @@ class _Slot:
             self.host_masks = torch.empty(nbytes, dtype=torch.uint8).pin_memory()
 
 
+class PackedMasks:
+    """The K masks of one sketch, bit-packed: `bits` is uint8 [K, H, ceil(W/8)], leftmost pixel in the MSB, rows padded to
+    whole bytes -- numpy.packbits(axis=-1) and the row layout of PIL mode "1", which is what the reference turns every mask
+    into right after run_SAM (InkLayer/runner.py:51, written as mask_{i}.png at :57-60)."""
+
+    __slots__ = ("bits", "height", "width")
+
+    def __init__(self, bits: np.ndarray, height: int, width: int) -> None:
+        self.bits, self.height, self.width = bits, height, width
+
+    def __len__(self) -> int:
+        return int(self.bits.shape[0])
+
+    def unpack(self) -> np.ndarray:
+        """np.bool_ [K, H, W]: the arrays run_SAM returns."""
+        if len(self) == 0:
+            return np.zeros((0, self.height, self.width), np.bool_)
+        return np.unpackbits(self.bits, axis=-1, count=self.width).view(np.bool_)
+
+    def to_pil(self, i: int):
+        """PIL mode "1" image of mask i, built from the packed rows without unpacking (runner.py:51)."""
+        from PIL import Image
+
+        return Image.frombytes("1", (self.width, self.height), self.bits[i].tobytes())
+
+
 class SketchSegmenter:
     """Batched, pipelined form of run_SAM for `main.py --dir`-style drivers (main.py:27-32 loops run_SAM per file).
 
@@ -51,10 +77,14 @@ class SketchSegmenter:
     pass.  `depth` batches are in flight: the pinned-memory H2D copy of batch i+1 and the D2H copy + host hand-off of
     batch i-1 run on their own streams / a worker thread under the kernels of batch i."""
 
-    def __init__(self, sam: Sam, max_batch: int = 8, depth: int = 2, copy_threads: int = 4) -> None:
+    def __init__(self, sam: Sam, max_batch: int = 8, depth: int = 2, copy_threads: int = 4, packed: bool = False) -> None:
+        """packed=True: results are `PackedMasks` (bit-packed by the post-process kernel: 8x less device->host traffic and
+        no host-side packing before the PNG hand-off) instead of np.bool_ arrays."""
         if sam.device.type != "cuda":
             raise RuntimeError("SketchSegmenter needs a Sam on a CUDA device")
         self.sam = sam
+        self.packed = packed
+        sam.reserve(max_batch, 128)  # workspace sized once: the per-slot encoder graphs never see it move
         self.transform = ResizeLongestSide(sam.image_encoder.img_size)
         self.max_batch = max_batch
         self.depth = max(1, depth)
@@ -95,7 +125,7 @@ class SketchSegmenter:
         tbs = [self.transform.apply_boxes_torch(torch.as_tensor(np.asarray(bx, dtype=np.float32).reshape(-1, 4)), sizes[i])
                for i, bx in enumerate(boxes)]
         hb = torch.cat(tbs).pin_memory() if sum(len(t) for t in tbs) else torch.zeros((0, 4))
-        total = sum(len(t) * s[0] * s[1] for t, s in zip(tbs, sizes))
+        total = sum(len(t) * s[0] * ((s[1] + 7) // 8 if self.packed else s[1]) for t, s in zip(tbs, sizes))
         slot.mask_buffers(max(total, 1), dev)
         caller = torch.cuda.current_stream(dev)
         self._s_in.wait_stream(caller)
@@ -120,7 +150,7 @@ class SketchSegmenter:
             feats = sam.encode(slot.dev_img[:B], in_sizes, graph=True)  # per-slot input buffer: replayed from a CUDA graph
             counts = [len(t) for t in tbs]
             splits = list(torch.split(db, counts)) if db.numel() else [db[:0] for _ in tbs]
-            _, _, _, offs = sam.decode_batch(feats, splits, in_sizes, sizes, masks_out=slot.dev_masks)
+            _, _, _, offs = sam.decode_batch(feats, splits, in_sizes, sizes, masks_out=slot.dev_masks, packed=self.packed)
             db.record_stream(self._s_run)
             slot.ev_done.record()
         with torch.cuda.stream(self._s_out):
@@ -136,8 +166,11 @@ class SketchSegmenter:
         slot.ev_out.synchronize()
         host = slot.host_masks.numpy()
 
-        def own(view) -> np.ndarray:
+        def own(view):
             off, k, (H, W) = view
+            if self.packed:
+                p = (W + 7) // 8
+                return PackedMasks(host[off:off + k * H * p].reshape(k, H, p).copy(), H, W)
             return host[off:off + k * H * W].view(np.bool_).reshape(k, H, W).copy()
 
         return list(self._copy_pool.map(own, slot.views))
@@ -146,8 +179,8 @@ class SketchSegmenter:
     @torch.no_grad()
     def segment_stream(self, batches: Iterable[Tuple[Sequence[np.ndarray], Sequence[np.ndarray]]]) -> Iterator[List[np.ndarray]]:
         """batches: iterable of (images, boxes) with up to max_batch sketches each (see segment_batch for the element
-        types).  Yields, in order, one list of bool arrays [K_i,H,W] per batch; results trail the input by `depth`
-        batches so that copies overlap compute."""
+        types).  Yields, in order, one list of bool arrays [K_i,H,W] (or PackedMasks, when built with packed=True) per
+        batch; results trail the input by `depth` batches so that copies overlap compute."""
         pending: deque = deque()
         for images, boxes in batches:
             assert len(images) == len(boxes)
@@ -193,7 +226,7 @@ def segmenter_for_checkpoint(sam_checkpoint: str, device="cuda", max_batch: int 
     key = (os.path.abspath(sam_checkpoint), str(device), max_batch)
     seg = _segmenters.get(key)
     if seg is None:
-        seg = SketchSegmenter(build_sam(checkpoint=sam_checkpoint).to(device), max_batch=max_batch)
+        seg = SketchSegmenter(build_sam(checkpoint=sam_checkpoint).to(device), max_batch=max_batch, packed=True)
         _segmenters[key] = seg
     return seg
 
@@ -211,4 +244,6 @@ def run_SAM(image_pil, boxes_filt, sam_checkpoint: Optional[str] = None, segment
     image = np.array(image_pil)[..., ::-1]  # the reference applies COLOR_BGR2RGB to an RGB array (sam.py:24-25)
     bx = boxes_filt.detach().cpu().numpy() if isinstance(boxes_filt, torch.Tensor) else np.asarray(boxes_filt)
     masks = segmenter.segment_batch([np.ascontiguousarray(image)], [bx])[0]
+    if isinstance(masks, PackedMasks):
+        masks = masks.unpack()
     return [m for m in masks]

@@ -160,7 +160,12 @@ def content_iou(inter: np.ndarray, bboxes: np.ndarray, scores: Sequence[float], 
 def sketch_nms(sketch_gray: np.ndarray, bboxes: np.ndarray, scores: np.ndarray, masks: Array, sketch_iou_threshold: float,
                bbox_iou_threshold: float = 0.7, device="cuda") -> np.ndarray:
     """nms_sketch.py:283-360.  sketch_gray: uint8 [H,W]; masks: [K,H,W] (what the reference keeps in masks/mask_{i}.png,
-    host or device).  Returns the kept ORIGINAL box indices in the reference's order."""
+    host or device).  Returns the kept ORIGINAL box indices in the reference's order.
+
+    Reference quirk, reproduced for drop-in parity: the reference calls content_iou with FILTERED indices and content_iou
+    opens `mask_{filtered index}.png` (nms_sketch.py:209-221,311-318) although the files were written under ORIGINAL
+    indices (runner.py:57-60); after filter_full_or_empty_bbox has dropped a box, filtered box f is therefore compared
+    through the mask of original box f, not kept[f].  tests/golden/refine_nms_drop_mid.npz pins this."""
     if len(bboxes) == 0:
         return np.array([])
     kept = filter_full_or_empty_bbox(sketch_gray, bboxes)
@@ -169,7 +174,7 @@ def sketch_nms(sketch_gray: np.ndarray, bboxes: np.ndarray, scores: np.ndarray, 
     h, w = sketch_gray.shape
     inter_all = content_iou_matrix(masks, sketch_gray, device).cpu().numpy()  # one K x K int32 D2H for all pairs
     fb, fs = bboxes[kept], scores[kept]
-    inter = inter_all[np.ix_(kept, kept)]
+    inter = inter_all[:len(kept), :len(kept)]  # mask_{f}.png for filtered index f (see the docstring)
     order = np.argsort(-fs)
     original_indices = kept[order]
     keep = np.ones(len(fb), dtype=bool)

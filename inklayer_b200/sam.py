@@ -281,12 +281,13 @@ class Sam:
 
     @torch.no_grad()
     def decode_batch(self, embeddings: torch.Tensor, boxes: Sequence[torch.Tensor], input_sizes: Sequence[Tuple[int, int]],
-                     original_sizes: Sequence[Tuple[int, int]], masks_out: Optional[torch.Tensor] = None):
+                     original_sizes: Sequence[Tuple[int, int]], masks_out: Optional[torch.Tensor] = None, packed: bool = False):
         """The boxes of B images in one pass of the decoder (the `main.py --dir` form of predict_torch).
         embeddings: float32 [B,256,64,64]; boxes[i]: [K_i,4] xyxy in image i's input frame (device or host).
         Returns (masks, iou [sum K], low_res [sum K,256,256], offsets) where `masks` is ONE flat uint8 device tensor
         holding image after image K_i maps of original_sizes[i] (written into `masks_out` when given) and
-        offsets[i] is image i's first element."""
+        offsets[i] is image i's first element.  packed=True: the maps are bit-packed, H x ceil(W/8) bytes each, leftmost
+        pixel in the MSB (numpy.packbits / PIL mode "1" rows, the form InkLayer/runner.py:51 converts masks to)."""
         h = self._require()
         dev, B = self.device, len(boxes)
         if embeddings.shape[0] != B or len(input_sizes) != B or len(original_sizes) != B:
@@ -299,7 +300,8 @@ class Sam:
         offsets, n = [], 0
         for i in range(B):
             offsets.append(n)
-            n += counts[i] * int(original_sizes[i][0]) * int(original_sizes[i][1])
+            H, W = int(original_sizes[i][0]), int(original_sizes[i][1])
+            n += counts[i] * H * ((W + 7) // 8 if packed else W)
         if all(b.device == dev for b in boxes):
             bx = torch.cat([b.reshape(-1, 4).to(torch.float32) for b in boxes]).contiguous()
         else:  # one pinned staging copy for all host boxes
@@ -313,9 +315,14 @@ class Sam:
         low = torch.empty((total, 256, 256), dtype=torch.float32, device=dev)
         if total > 0:
             with torch.cuda.device(dev):
-                _lib.check(_lib.load().inksam_decode_batch(
-                    h, _ptr(emb), B, _ptr(bx), counts, in_hw, or_hw, _ptr(masks_out), _ptr(iou), _ptr(low), _ptr(None),
-                    ctypes.c_float(self.mask_threshold), _stream(dev)))
+                if packed:
+                    _lib.check(_lib.load().inksam_decode_batch_packed(
+                        h, _ptr(emb), B, _ptr(bx), counts, in_hw, or_hw, _ptr(masks_out), _ptr(iou), _ptr(low),
+                        ctypes.c_float(self.mask_threshold), _stream(dev)))
+                else:
+                    _lib.check(_lib.load().inksam_decode_batch(
+                        h, _ptr(emb), B, _ptr(bx), counts, in_hw, or_hw, _ptr(masks_out), _ptr(iou), _ptr(low), _ptr(None),
+                        ctypes.c_float(self.mask_threshold), _stream(dev)))
         return masks_out, iou, low, offsets
 
     @torch.no_grad()

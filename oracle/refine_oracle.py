@@ -110,7 +110,12 @@ def pair_scores(inter: np.ndarray, bboxes: np.ndarray, scores: np.ndarray, i: in
 def sketch_nms_from_matrix(inter: np.ndarray, bboxes: np.ndarray, scores: np.ndarray, kept: np.ndarray, h: int, w: int,
                            sketch_iou_threshold: float, bbox_iou_threshold: float = 0.7) -> np.ndarray:
     """The greedy loop of sketch_nms (nms_sketch.py:283-360) after filter_full_or_empty_bbox has produced `kept`
-    (indices into bboxes); `inter` is indexed by ORIGINAL mask index (mask_{i}.png)."""
+    (indices into bboxes); `inter` is indexed by ORIGINAL mask index (mask_{i}.png).
+
+    Reference quirk, reproduced: sketch_nms hands content_iou the FILTERED boxes and FILTERED indices
+    (nms_sketch.py:295-296,311-318), and content_iou opens `mask_{box_index}.png` with that filtered index
+    (nms_sketch.py:209-221) while runner.py:57-60 wrote the files under ORIGINAL indices.  So once the filter has dropped
+    a box, filtered box f is compared through the mask file of original box f, not kept[f]."""
     if len(kept) == 0:
         return np.array([])
     fb, fs = bboxes[kept], scores[kept]
@@ -118,7 +123,7 @@ def sketch_nms_from_matrix(inter: np.ndarray, bboxes: np.ndarray, scores: np.nda
     original = kept[order]
     n = len(fb)
     keep = np.ones(n, dtype=bool)
-    sub = inter[np.ix_(kept, kept)]
+    sub = inter[:n, :n]  # mask_{f}.png for filtered index f
     for i in range(n):
         if not keep[i]:
             continue

@@ -38,8 +38,10 @@ def make_clean(name, H, W, K, seed):
     print(name, masks.shape, "kept fraction", (out > 0).sum() / max((masks > 127).sum(), 1))
 
 
-def make_nms(name, H, W, K, seed, thr):
+def make_nms(name, H, W, K, seed, thr, full_box_at=None):
     masks, sketch, bboxes, scores = refine_case(seed, K, H, W)
+    if full_box_at is not None:  # a box covering the whole sketch in the MIDDLE of the list: dropped by
+        bboxes[full_box_at] = [0, 0, W - 1, H - 1]  # filter_full_or_empty_bbox, so filtered and original indices diverge
     with tempfile.TemporaryDirectory() as d:
         sp = os.path.join(d, "input.png")
         Image.fromarray(sketch).save(sp)
@@ -52,6 +54,7 @@ def make_nms(name, H, W, K, seed, thr):
             pairs = [(i, j) for i in range(K) for j in range(i + 1, K)][:: max(1, K // 3)]
             vals = [content_iou(sp, bboxes, scores, i, j, md) for i, j in pairs]
     np.savez_compressed(os.path.join(HERE, f"refine_nms_{name}.npz"), shape=np.array(masks.shape), seed=seed, thr=thr,
+                        full_box_at=np.int64(-1 if full_box_at is None else full_box_at),
                         keep=np.asarray(keep, dtype=np.int64), pairs=np.array(pairs), sketch_iou=np.array([v[0] for v in vals]),
                         bbox_iou=np.array([v[1] for v in vals]), better=np.array([v[2] for v in vals]))
     print(name, "keep", keep)
@@ -63,3 +66,4 @@ if __name__ == "__main__":
     make_clean("1024x1000", 1024, 1000, 2, 13)
     make_nms("512_k12", 512, 512, 12, 21, 0.2)
     make_nms("600x750_k9", 600, 750, 9, 22, 0.5)
+    make_nms("drop_mid", 512, 640, 12, 23, 0.2, full_box_at=3)

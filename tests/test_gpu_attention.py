@@ -49,10 +49,14 @@ def test_global_attention(hd, heads, B):
     assert rel_err(out, ref) < 1.5e-2
 
 
-@pytest.mark.parametrize("hd,peak_at", [(80, 3000), (64, 70), (80, 4095)])
-def test_global_attention_late_peak_rescales(hd, peak_at):
-    """The lazy softmax shift comes from the first 32 keys; a much later key whose score is ~40 log2 units above it
-    (probability ratio 2^40) must trigger the exact rescale of the running sum and of the O accumulator in TMEM."""
+@pytest.mark.parametrize("hd,peak_at,gain", [(80, 3000, 50.0), (64, 70, 50.0), (80, 4095, 50.0),
+                                             (80, 3000, 170.0), (64, 40, 170.0), (80, 4095, 400.0), (64, 2047, 400.0)])
+def test_global_attention_late_peak_rescales(hd, peak_at, gain):
+    """The lazy softmax shift comes from the first 32 keys.  A later key ~40 log2 units above it (gain 50) must trigger
+    the exact rescale of the running sum and of the O accumulator in TMEM; a key 137 / 320+ log2 units above it (gain
+    170 / 400) is beyond the 2^120 exponent clamp of the hot loop and must take the cold path that raises the shift to
+    the sub-tile's true maximum BEFORE its probabilities are used (the clamp must never bite silently).  A
+    second, lower peak 1000 keys earlier makes the shift move twice."""
     lib = _lib.load()
     heads, B = 2, 1
     g = torch.Generator().manual_seed(7 + hd + peak_at)
@@ -60,7 +64,9 @@ def test_global_attention_late_peak_rescales(hd, peak_at):
     u = torch.ones(hd) / hd ** 0.5
     t = torch.randn(3, B, heads, 4096, hd, generator=g) * 1.0
     t[0] += 5.0 * u                       # every query has a component along u
-    t[1, :, :, peak_at] += 50.0 * u       # one key far along u: score about 5 * 50 / sqrt(hd) nats above the rest
+    t[1, :, :, peak_at] += gain * u       # one key far along u: score about 5 * gain / sqrt(hd) nats above the rest
+    if peak_at >= 1000:
+        t[1, :, :, peak_at - 1000] += 0.5 * gain * u
     qkv = t.permute(1, 3, 0, 2, 4).reshape(B * 4096, 3 * D).to(torch.bfloat16)
     rel_h = (torch.randn(127, hd, generator=g) * 0.1).to(torch.bfloat16).float()
     rel_w = (torch.randn(127, hd, generator=g) * 0.1).to(torch.bfloat16).float()
@@ -95,6 +101,34 @@ def test_window_attention(hd, heads, B):
     torch.cuda.synchronize()
     t = win.cuda().reshape(B * 25, 196, 3, heads, hd).permute(2, 0, 3, 1, 4).reshape(3, B * 25 * heads, 196, hd)
     ref = ref_attention(t[0], t[1], t[2], rel_h.cuda(), rel_w.cuda(), 14)
+    ref = ref.reshape(B * 25, heads, 14, 14, hd).permute(0, 2, 3, 1, 4).reshape(B * 25, 14, 14, D)
+    ref = O.window_unpartition(ref, 14, 70, 64).reshape(B * 4096, D)
+    assert torch.isfinite(out.float()).all()
+    assert rel_rms(out, ref) < 1e-2
+    assert rel_err(out, ref) < 1.5e-2
+
+
+@pytest.mark.parametrize("hd,peak_key,gain", [(80, 150, 170.0), (64, 195, 400.0), (80, 40, 50.0)])
+def test_window_attention_late_peak(hd, peak_key, gain):
+    """Windowed blocks with one key of every window far above the others (beyond the first 32 keys and, for gain >= 170,
+    more than 120 log2 units above them): the softmax must stay exact (the reference subtracts the true row maximum)."""
+    lib = _lib.load()
+    heads, B = 2, 1
+    g = torch.Generator().manual_seed(300 + hd + peak_key)
+    D = heads * hd
+    u = torch.ones(hd) / hd ** 0.5
+    t = torch.randn(3, B * 25, heads, 196, hd, generator=g)
+    t[0] += 5.0 * u
+    t[1, :, :, peak_key] += gain * u
+    win = t.permute(1, 3, 0, 2, 4).reshape(B * 25, 196, 3 * D).to(torch.bfloat16).float()
+    rel_h = (torch.randn(27, hd, generator=g) * 0.3).to(torch.bfloat16).float()
+    rel_w = (torch.randn(27, hd, generator=g) * 0.3).to(torch.bfloat16).float()
+    qd = win.reshape(B * 25 * 196, 3 * D).to(torch.bfloat16).cuda()
+    out = torch.zeros(B * 4096, D, dtype=torch.bfloat16, device="cuda")
+    _lib.check(lib.inksam_op_attention(1, ptr(qd), ptr(rel_table(rel_h, rel_w, 64)), ptr(out), B, heads, hd, stream()))
+    torch.cuda.synchronize()
+    tt = win.cuda().reshape(B * 25, 196, 3, heads, hd).permute(2, 0, 3, 1, 4).reshape(3, B * 25 * heads, 196, hd)
+    ref = ref_attention(tt[0], tt[1], tt[2], rel_h.cuda(), rel_w.cuda(), 14)
     ref = ref.reshape(B * 25, heads, 14, 14, hd).permute(0, 2, 3, 1, 4).reshape(B * 25, 14, 14, D)
     ref = O.window_unpartition(ref, 14, 70, 64).reshape(B * 4096, D)
     assert torch.isfinite(out.float()).all()

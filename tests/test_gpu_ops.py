@@ -119,6 +119,35 @@ def test_postprocess_matches_interpolate(inp, orig):
         assert (buf[:shift] == 7).all() and (buf[shift + K * H * W:] == 7).all()  # nothing written outside
 
 
+@pytest.mark.parametrize("inp,orig", [((1024, 1024), (1024, 1024)), ((819, 1024), (600, 750)), ((1024, 1024), (750, 750)),
+                                      ((1024, 577), (1333, 751)), ((1024, 683), (300, 200)), ((1024, 640), (2048, 1280)),
+                                      ((1024, 1001), (1024, 1001)), ((3, 1024), (3, 1024)), ((1024, 16), (1024, 16)),
+                                      ((1024, 5), (17, 5)), ((1024, 1024), (33, 1031))])
+def test_postprocess_packed_is_packbits_of_the_byte_masks(inp, orig):
+    """The bit-packed output format (one bit per pixel, MSB first, rows padded to whole bytes -- numpy.packbits / PIL mode
+    "1" rows, InkLayer/runner.py:51) holds exactly the bits of the byte masks, for the fast and the general path, odd
+    widths, at a misaligned base address, and nothing is written outside [K][H][ceil(W/8)]."""
+    import numpy as np
+
+    lib = _lib.load()
+    K = 3
+    low = (torch.randn(K, 1, 256, 256, generator=torch.Generator().manual_seed(9)) * 0.1).cuda()
+    H, W = orig
+    pitch = (W + 7) // 8
+    masks = torch.empty(K, H, W, dtype=torch.uint8, device="cuda")
+    _lib.check(lib.inksam_op_postprocess(ptr(low), ptr(masks), None, K, inp[0], inp[1], H, W, ctypes.c_float(0.0), stream()))
+    want = np.packbits(masks.cpu().numpy().astype(bool), axis=-1)
+    assert want.shape == (K, H, pitch)
+    for shift in (0, 16, 3):
+        buf = torch.full((K * H * pitch + 64,), 0xA5, dtype=torch.uint8, device="cuda")
+        _lib.check(lib.inksam_op_postprocess_packed(ptr(low), buf.data_ptr() + shift, K, inp[0], inp[1], H, W,
+                                                    ctypes.c_float(0.0), stream()))
+        got = buf[shift:shift + K * H * pitch].view(K, H, pitch).cpu().numpy()
+        np.testing.assert_array_equal(got, want)
+        assert (buf[:shift] == 0xA5).all() and (buf[shift + K * H * pitch:] == 0xA5).all()
+    assert np.array_equal(np.unpackbits(want, axis=-1, count=W), masks.cpu().numpy())
+
+
 @pytest.mark.parametrize("hw", [(750, 750), (600, 750), (300, 200), (1333, 751), (2000, 1500), (64, 1000), (37, 53), (1025, 1024),
                                 (1, 7), (777, 3001), (1024, 512)])
 def test_resize_u8_bit_exact_with_pillow_oracle(hw):

@@ -64,3 +64,30 @@ def test_preprocess_shape_rounding():
     assert O.preprocess_shape(600, 750, 1024) == (819, 1024)
     assert O.preprocess_shape(1024, 512, 1024) == (1024, 512)
     assert O.preprocess_shape(333, 1000, 1024) == (341, 1024)
+
+
+def test_reference_copy_agrees_with_the_port():
+    """oracle/_ref (the unmodified vendored segment_anything placed by oracle/install_ref.py; it is what bench.py's CPU arm
+    times, kind "reference") and the port agree on tiny_1024: same embedding, logits and masks to fp32 summation order."""
+    from oracle import ref_loader
+
+    if not ref_loader.available():
+        pytest.skip("oracle/_ref absent: run `python oracle/install_ref.py` where /root/reference exists")
+    from inklayer_b200.config import CONFIGS
+
+    cfg_name, seed, img, boxes = golden_case_inputs("tiny_1024")
+    sd = synthetic_state_dict(CONFIGS[cfg_name], seed)
+    ref = ref_loader.reference_predictor(CONFIGS[cfg_name], sd)
+    with torch.no_grad():
+        ref.set_image(img)
+        tb = ref.transform.apply_boxes_torch(torch.from_numpy(boxes), img.shape[:2])
+        m_ref, i_ref, l_ref = ref.predict_torch(None, None, boxes=tb, multimask_output=False)
+    port = O.OraclePredictor(O.CONFIGS[cfg_name], sd)
+    port.set_image(img)
+    m, i, l = port.predict_torch(O.apply_boxes(torch.from_numpy(boxes), img.shape[:2]))
+    np.testing.assert_allclose(port.features.numpy(), ref.features.numpy(), atol=2e-4, rtol=0)
+    np.testing.assert_allclose(l.numpy(), l_ref.numpy(), atol=2e-5, rtol=0)
+    np.testing.assert_allclose(i.numpy(), i_ref.numpy(), atol=1e-5, rtol=0)
+    assert mask_iou(m.numpy(), m_ref.numpy()).min() > 0.9999
+    gold = load_golden("tiny_1024")  # and the copy reproduces the committed vectors it was pinned by
+    np.testing.assert_allclose(l_ref.numpy()[: gold["low"].shape[0]], gold["low"], atol=1e-6, rtol=0)
