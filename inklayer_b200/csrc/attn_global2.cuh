@@ -35,7 +35,7 @@ struct AttnGlobal2 {
   static constexpr int THREADS = 352;
 };
 
-template <int HD>
+template <int HD, int KPOLY>
 __global__ void __launch_bounds__(352, 1)
 attn_global2_kernel(const __grid_constant__ CUtensorMap tm64, const __grid_constant__ CUtensorMap tm16,
                     const __grid_constant__ CUtensorMap tr64, const __grid_constant__ CUtensorMap tr16, const AttnArgs a) {
@@ -46,10 +46,7 @@ attn_global2_kernel(const __grid_constant__ CUtensorMap tm64, const __grid_const
   constexpr uint32_t IDESC_S = make_idesc(1u, 128, 64);
   constexpr int NT = 32;   // key tiles of 128 (TMA / smem ring granularity)
   constexpr int NS = 64;   // sub-tiles of 64 keys (MMA / softmax granularity)
-#ifndef INKSAM_KPOLY
-#define INKSAM_KPOLY 8
-#endif
-  constexpr int kPoly = INKSAM_KPOLY;  // keys per sub-tile whose exp2 runs on the FMA pipe (even, <= 32)
+  constexpr int kPoly = KPOLY;  // keys per sub-tile whose exp2 runs on the FMA pipe (even, <= 32)
 
   extern __shared__ uint8_t smem_raw[];
   const uint32_t smem_base = (smem_u32(smem_raw) + 1023u) & ~1023u;
@@ -263,7 +260,9 @@ attn_global2_kernel(const __grid_constant__ CUtensorMap tm64, const __grid_const
       for (int i = 0; i < 32; i += 2) {
         float x0, x1;
         f2_unpack(f2_fma(f2_pack(__uint_as_float(v0[i]), __uint_as_float(v0[i + 1])), c12, f2_add(bW2[i >> 1], bb2)), x0, x1);
-        const float p0 = ex2_approx(fminf(x0, 120.f)), p1 = ex2_approx(fminf(x1, 120.f));
+        // no clamp: a key more than 128 log2 units above the shift gives +inf, which makes the sub-tile's sum +inf and
+        // sends it through the cold path below, where the shift is raised and the sub-tile is exponentiated again
+        const float p0 = ex2_approx(x0), p1 = ex2_approx(x1);
         l2 = f2_add(l2, f2_pack(p0, p1));
         pk[i >> 1] = pack_bf16x2(p0, p1);
       }
@@ -274,10 +273,10 @@ attn_global2_kernel(const __grid_constant__ CUtensorMap tm64, const __grid_const
         float x0, x1;
         f2_unpack(f2_fma(f2_pack(__uint_as_float(v1[i]), __uint_as_float(v1[i + 1])), c12, f2_add(bW2[16 + (i >> 1)], bb2)), x0, x1);
         float p0, p1;
-        if (i >= 32 - kPoly) {
-          f2_unpack(f2_exp2_poly(f2_pack(fmaxf(fminf(x0, 120.f), -126.f), fmaxf(fminf(x1, 120.f), -126.f))), p0, p1);
+        if (i >= 32 - kPoly) {  // the polynomial needs its argument in [-126, 126]; 126 still trips the cold path (sum >= 2^100)
+          f2_unpack(f2_exp2_poly(f2_pack(fmaxf(fminf(x0, 126.f), -126.f), fmaxf(fminf(x1, 126.f), -126.f))), p0, p1);
         } else {
-          p0 = ex2_approx(fminf(x0, 120.f)); p1 = ex2_approx(fminf(x1, 120.f));
+          p0 = ex2_approx(x0); p1 = ex2_approx(x1);
         }
         l2 = f2_add(l2, f2_pack(p0, p1));
         pk[16 + (i >> 1)] = pack_bf16x2(p0, p1);
@@ -289,12 +288,12 @@ attn_global2_kernel(const __grid_constant__ CUtensorMap tm64, const __grid_const
         lsub = la + lb;
         l2 = f2_pack(0.f, 0.f);
       }
-      // The exponent is clamped at 120 above so that a key far above the shift cannot produce inf.  A sub-tile whose sum
-      // reaches 2^100 holds a key more than 94 log2 units above the shift, i.e. possibly a CLAMPED one: before P(t) is
-      // handed to the tensor cores the shift is raised to this sub-tile's true maximum, everything accumulated so far is
-      // rescaled by the exact power of two, and the sub-tile is exponentiated again.  Exact for any logit range; cold.
-      if (__any_sync(0xffffffffu, lsub > 1.2676506e30f)) {
-        const bool hot = lsub > 1.2676506e30f;
+      // A sub-tile whose sum reaches 2^100 (or overflowed to +inf; !(x <= c) also catches NaN) holds a key more than 94
+      // log2 units above the shift: before P(t) is handed to the tensor cores the shift is raised to this sub-tile's true
+      // maximum, everything accumulated so far is rescaled by the exact power of two, and the sub-tile is exponentiated
+      // again.  Exact for any logit range; cold.
+      if (__any_sync(0xffffffffu, !(lsub <= 1.2676506e30f))) {
+        const bool hot = !(lsub <= 1.2676506e30f);
         float mx = -INFINITY;
 #pragma unroll
         for (int i = 0; i < 32; i += 2) {

@@ -81,8 +81,20 @@ def test_global_attention_late_peak_rescales(hd, peak_at, gain):
     assert rel_err(out, ref) < 1.5e-2
 
 
-@pytest.mark.parametrize("hd,heads,B", [(64, 2, 1), (80, 2, 1), (80, 3, 2)])
-def test_window_attention(hd, heads, B):
+@pytest.fixture(params=["v4", "v4-kpoly8", "v3", "v2"])
+def window_kernel(request, monkeypatch):
+    """The windowed kernel variants (read per launch by attn_host.cu): the current one with its default / no / double
+    share of polynomial exp2, and the previous kernel as a cross-check."""
+    monkeypatch.delenv("INKSAM_WINDOW_ATTN", raising=False)
+    monkeypatch.delenv("INKSAM_WINDOW_KPOLY", raising=False)
+    monkeypatch.setenv("INKSAM_WINDOW_ATTN", request.param[1])
+    if "-kpoly" in request.param:
+        monkeypatch.setenv("INKSAM_WINDOW_KPOLY", request.param.split("-kpoly")[1])
+    return request.param
+
+
+@pytest.mark.parametrize("hd,heads,B", [(64, 2, 1), (80, 2, 1), (80, 3, 2), (80, 16, 1), (64, 12, 3)])
+def test_window_attention(hd, heads, B, window_kernel):
     """Windowed blocks: 14x14 windows over the zero-padded 70x70 grid; padded tokens carry the qkv bias and are NOT
     masked (SA/modeling/image_encoder.py:170-177,243-289)."""
     lib = _lib.load()
@@ -108,11 +120,13 @@ def test_window_attention(hd, heads, B):
     assert rel_err(out, ref) < 1.5e-2
 
 
-@pytest.mark.parametrize("hd,peak_key,gain", [(80, 150, 170.0), (64, 195, 400.0), (80, 40, 50.0)])
-def test_window_attention_late_peak(hd, peak_key, gain):
-    """Windowed blocks with one key of every window far above the others (beyond the first 32 keys and, for gain >= 170,
-    more than 120 log2 units above them): the softmax must stay exact (the reference subtracts the true row maximum)."""
+@pytest.mark.parametrize("hd,peak_key,gain", [(80, 150, 170.0), (64, 195, 400.0), (80, 40, 50.0), (64, 97, 170.0), (80, 98, 400.0)])
+def test_window_attention_late_peak(hd, peak_key, gain, monkeypatch):
+    """Windowed blocks with two keys of every window far above the others (beyond the first 32 keys and, for gain >= 170,
+    more than 120 log2 units above them, 7 log2 units apart): the softmax must stay exact -- the reference subtracts the
+    true row maximum.  (A kernel that clamps the exponent gives both keys the same weight and fails this.)"""
     lib = _lib.load()
+    monkeypatch.setenv("INKSAM_WINDOW_ATTN", "4")
     heads, B = 2, 1
     g = torch.Generator().manual_seed(300 + hd + peak_key)
     D = heads * hd
@@ -120,6 +134,7 @@ def test_window_attention_late_peak(hd, peak_key, gain):
     t = torch.randn(3, B * 25, heads, 196, hd, generator=g)
     t[0] += 5.0 * u
     t[1, :, :, peak_key] += gain * u
+    t[1, :, :, (peak_key + 61) % 196] += 0.95 * gain * u   # a second peak in the other key half, a few log2 units lower
     win = t.permute(1, 3, 0, 2, 4).reshape(B * 25, 196, 3 * D).to(torch.bfloat16).float()
     rel_h = (torch.randn(27, hd, generator=g) * 0.3).to(torch.bfloat16).float()
     rel_w = (torch.randn(27, hd, generator=g) * 0.3).to(torch.bfloat16).float()

@@ -4,6 +4,7 @@
     tools/ncu_summary.py launches gpurun_out/launches.csv            # per-kernel totals of a launch list
     tools/ncu_summary.py full gpurun_out/prof_gemm.ncu-rep [...]     # key metrics of every launch in --set full reports
     tools/ncu_summary.py traffic gpurun_out/prof_gemm.ncu-rep out.json  # mean DRAM bytes per launch (bench.py roofline.traffic)
+    tools/ncu_summary.py decoder-traffic gpurun_out/dec_traffic.csv out.json  # DRAM bytes of one decode pass (bench.py decoder.hbm_gbs)
 """
 import collections
 import csv
@@ -88,10 +89,45 @@ def traffic(path: str, out_json: str) -> None:
     print(f"{len(per)} launches, mean DRAM traffic {mean / 1e6:.1f} MB per launch -> {out_json}")
 
 
+def decoder_traffic(path: str, out_json: str) -> None:
+    """Sum of dram__bytes_read.sum + dram__bytes_write.sum (and of gpu__time_duration.sum) over every launch of ONE decode
+    pass: `ncu --csv --metrics dram__bytes_read.sum,dram__bytes_write.sum,gpu__time_duration.sum --profile-from-start off`
+    around tools/decode_pass.py.  bench.py divides the byte total by the pass's live CUDA-event time (decoder.hbm_gbs)."""
+    import json
+
+    lines = [l for l in open(path) if l.startswith('"')]
+    r = csv.reader(lines)
+    hdr = next(r)
+    ix = {h: i for i, h in enumerate(hdr)}
+    scale = {"byte": 1.0, "Kbyte": 1e3, "Mbyte": 1e6, "Gbyte": 1e9, "ns": 1e-3, "nsecond": 1e-3, "us": 1.0, "usecond": 1.0,
+             "ms": 1e3, "msecond": 1e3}
+    per = collections.OrderedDict()
+    for row in r:
+        if len(row) < len(hdr):
+            continue
+        key = (row[ix["ID"]], short(row[ix["Kernel Name"]]))
+        d = per.setdefault(key, {"bytes": 0.0, "us": 0.0})
+        v = float(row[ix["Metric Value"]].replace(",", "")) * scale.get(row[ix["Metric Unit"]], 1.0)
+        if row[ix["Metric Name"]].startswith("dram__bytes"):
+            d["bytes"] += v
+        elif row[ix["Metric Name"]].startswith("gpu__time_duration"):
+            d["us"] += v
+    agg = collections.OrderedDict()
+    for (_, k), d in per.items():
+        a = agg.setdefault(k, {"kernel": k, "launches": 0, "bytes": 0.0, "us": 0.0})
+        a["launches"] += 1; a["bytes"] += d["bytes"]; a["us"] += d["us"]
+    total = sum(d["bytes"] for d in per.values())
+    json.dump({"source": path, "launches": len(per), "dram_bytes_per_pass": total, "ncu_us_per_pass": sum(d["us"] for d in per.values()),
+               "per_kernel": sorted(agg.values(), key=lambda a: -a["bytes"])}, open(out_json, "w"), indent=1)
+    print(f"{len(per)} launches, DRAM traffic {total / 1e6:.1f} MB per decode pass -> {out_json}")
+
+
 if __name__ == "__main__":
     if sys.argv[1] == "launches":
         launches(sys.argv[2])
     elif sys.argv[1] == "traffic":
         traffic(sys.argv[2], sys.argv[3])
+    elif sys.argv[1] == "decoder-traffic":
+        decoder_traffic(sys.argv[2], sys.argv[3])
     else:
         full(sys.argv[2:])
