@@ -48,6 +48,10 @@ int inksam_op_gemm(int cg, int tf32, int bn, int epi, const void* A, int lda, co
  * out: bf16 [B*4096][D] in token order. */
 int inksam_op_attention(int windowed, const void* qkv, const void* rel, void* out, int B, int heads, int head_dim, void* stream);
 
+/* Debug / profiling aid: buf = device array of [items][16] int64 that CTA 0 of the windowed attention kernel fills with
+ * the clock64() of its pipeline events (MMA issue, barrier hand-offs) on the following launches; NULL switches it off. */
+int inksam_op_attention_trace(long long* buf);
+
 /* nn.LayerNorm over the last dim (fp32 in, bf16 out); plain != 0 only casts. image_encoder.py:168,180. */
 int inksam_op_layernorm(const float* x, const float* w, const float* b, void* out, int M, int D, float eps, int plain, void* stream);
 

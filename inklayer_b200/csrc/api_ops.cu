@@ -31,6 +31,11 @@ int inksam_op_attention(int windowed, const void* qkv, const void* rel, void* ou
   return launch_attention(windowed, qkv, rel, out, B, heads, head_dim, static_cast<cudaStream_t>(stream));
 }
 
+int inksam_op_attention_trace(long long* buf) {
+  set_attention_trace(buf);
+  return 0;
+}
+
 int inksam_op_layernorm(const float* x, const float* w, const float* b, void* out, int M, int D, float eps, int plain, void* stream) {
   return launch_layernorm_bf16(x, w, b, out, M, D, eps, plain, nullptr, static_cast<cudaStream_t>(stream));
 }

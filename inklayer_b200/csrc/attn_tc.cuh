@@ -31,6 +31,7 @@ struct AttnArgs {
   int B, heads, D;      // images, heads, embed dim
   float c1;             // head_dim^-0.5 * log2(e)
   __nv_bfloat16* out;   // [B*4096][D] bf16, natural token order, heads concatenated
+  long long* trace;     // optional (debug): clock64() of pipeline events of CTA 0, [item][16] (inksam_op_attention_trace)
 };
 
 constexpr float kLog2e = 1.4426950408889634f;

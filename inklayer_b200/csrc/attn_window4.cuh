@@ -10,15 +10,20 @@
 // on one item at a time and lost the overlap of two independent chains.  Here:
 //
 //   warp 17      TMA producer: rel-pos table once; per (image, window, head) pair Q(mt=0), K, Q(mt=1), V into 2-slot rings
-//   warp 16      MMA issuer (one thread); per item n (128 query rows: mt = n & 1 -> rows 0..127 / 128..195 of the window):
-//                T(n) = Q REL^T -> TMEM columns [416,480);  S(n) = Q K^T -> S buffer n & 1;  then PV(n-1)
+//   warp 16      MMA issuer 1 (one thread); per item n (128 query rows: mt = n & 1 -> rows 0..127 / 128..195 of the window):
+//                S(n) = Q K^T + [bias] E^T -> S buffer n & 1;  T(n+1) = Q REL^T -> TMEM columns [416,480), up to two items
+//                ahead of its softmax
+//   warp 18      MMA issuer 2 (one thread): O(n) = P V.  (40 tcgen05.mma per item saturate one issuing thread.)
 //   warps 8-11   bias warps (one per TMEM lane quarter): read T(n), gather this query's 14 + 14 decomposed rel-pos terms
-//                (q . rel_pos_h[qh - kh + 13], q . rel_pos_w[qw - kw + 13], on the UNSCALED q: image_encoder.py:234,354-355)
-//                into shared memory, in log2 units
+//                (q . rel_pos_h[qh - kh + 13], q . rel_pos_w[qw - kw + 13], on the UNSCALED q: image_encoder.py:234,354-355),
+//                split each into a bf16 high and low half (together exact to 2^-17) and store them as a 128 x 64 bf16
+//                MMA operand into TMEM columns [480,512): the issuer adds them to S on the tensor cores with one more
+//                K = 64 MMA against a constant 0/1 selection matrix E (key = 14 kh + kw selects bias_h[kh] and bias_w[kw]),
+//                so the softmax warps spend no instruction and no register on the bias
 //   warps 0-3    softmax group A: even items, S buffer 0      warps 4-7  softmax group B: odd items, S buffer 1
 //                thread = query row = TMEM lane.  Two passes over the 196 logits of the row: the TRUE row maximum first
-//                (as the reference softmax; exact for any logit range, nothing is clamped), then exp2(x - max), P (bf16)
-//                over the first 104 columns of the S buffer, the row sum to shared memory
+//                (as the reference softmax; exact for any logit range, nothing is clamped), then exp2(c1 (s - max)), P
+//                (bf16) over the first 104 columns of the S buffer, the row sum to shared memory: 3 instructions per key
 //   warps 12-15  epilogue warps: O(n) = P V (columns 112..191 of the S buffer) / row sum -> bf16 -> natural token order
 //                (window_unpartition: padded rows / columns are dropped, image_encoder.py:287-288)
 // The chain of a softmax group is  S(n) -> softmax -> PV(n) -> O read -> S(n+2);  T, the bias gather and the store of O
@@ -26,7 +31,7 @@
 // The qkv matrix is in window order with the qkv bias in the rows of padded tokens (the reference zero-pads AFTER norm1:
 // padded tokens carry q = k = v = bias and are NOT masked, image_encoder.py:258-259).  Keys = the window's 196 tokens in
 // one 208-row TMA box (rows 196..207 belong to the next window and get P = 0).
-// TMEM (512 columns, the whole SM): S0 [0,208)  S1 [208,416)  T [416,480).
+// TMEM (512 columns, the whole SM): S0 [0,208)  S1 [208,416)  T [416,480)  bias operand [480,512).
 #pragma once
 #include "attn_window3.cuh"
 
@@ -37,17 +42,17 @@ struct AttnWindow4 {
   static constexpr int QT = AttnTile<HD>::bytes(128);   // 20480 / 16384
   static constexpr int KT = AttnTile<HD>::bytes(208);   // 33792 / 26624
   static constexpr int RT = 64 * 128 + (HD == 80 ? 64 * 32 : 0);  // rel table, 64 rows
+  static constexpr int ET = 208 * 128;                   // selection matrix E: 208 key rows x 64 bf16, 128B swizzle
   static constexpr int OFF_Q = 0, OFF_K = 2 * QT, OFF_V = 2 * QT + 2 * KT, OFF_R = 2 * QT + 4 * KT;
-  static constexpr int BIAS_PITCH = 29;                  // floats per row: bias_h[14], bias_w[14] (+1: conflict-free)
-  static constexpr int OFF_BIAS = ((OFF_R + RT + 1023) / 1024) * 1024;   // [2][128][29] floats
-  static constexpr int OFF_L = OFF_BIAS + 2 * 128 * BIAS_PITCH * 4;      // row sums [2][128] floats
-  static constexpr int OFF_BAR = ((OFF_L + 2 * 128 * 4 + 127) / 128) * 128;
+  static constexpr int OFF_E = ((OFF_R + RT + 1023) / 1024) * 1024;
+  static constexpr int OFF_L = OFF_E + ET;               // row sums [2][128] floats
+  static constexpr int OFF_BAR = OFF_L + 2 * 128 * 4;
   static constexpr int SMEM_BYTES = OFF_BAR + 256 + 1024;
-  static constexpr int THREADS = 576;
+  static constexpr int THREADS = 608;
 };
 
 template <int HD, int KPOLY>
-__global__ void __launch_bounds__(576, 1)
+__global__ void __launch_bounds__(608, 1)
 attn_window4_kernel(const __grid_constant__ CUtensorMap tq64, const __grid_constant__ CUtensorMap tq16,
                     const __grid_constant__ CUtensorMap tk64, const __grid_constant__ CUtensorMap tk16,
                     const __grid_constant__ CUtensorMap tr64, const __grid_constant__ CUtensorMap tr16, const AttnArgs a,
@@ -55,7 +60,7 @@ attn_window4_kernel(const __grid_constant__ CUtensorMap tq64, const __grid_const
   using L = AttnWindow4<HD>;
   constexpr uint32_t IDESC_S = make_idesc(1u, 128, 208);
   constexpr uint32_t IDESC_T = make_idesc(1u, 128, 64);
-  constexpr uint32_t S_STRIDE = 208, T_COL = 416, O_COL = 112;
+  constexpr uint32_t S_STRIDE = 208, T_COL = 416, B_COL = 480, O_COL = 112;
   static_assert(KPOLY % 2 == 0 && KPOLY >= 0 && KPOLY <= 32, "KPOLY: keys per 32-key chunk on the FMA-pipe exp2");
 
   extern __shared__ uint8_t smem_raw[];
@@ -65,7 +70,7 @@ attn_window4_kernel(const __grid_constant__ CUtensorMap tq64, const __grid_const
   auto k64 = [&](int s) { return smem_base + L::OFF_K + s * L::KT; };
   auto v64 = [&](int s) { return smem_base + L::OFF_V + s * L::KT; };
   const uint32_t r64 = smem_base + L::OFF_R, r16 = r64 + 64 * 128;
-  float* bias_sm = reinterpret_cast<float*>(smem_gen + L::OFF_BIAS);
+  const uint32_t e64 = smem_base + L::OFF_E;
   float* lsum_sm = reinterpret_cast<float*>(smem_gen + L::OFF_L);
   const uint32_t bar0 = smem_base + L::OFF_BAR;
   auto bar_qfull = [&](int s) { return bar0 + 8 * s; };
@@ -73,12 +78,12 @@ attn_window4_kernel(const __grid_constant__ CUtensorMap tq64, const __grid_const
   auto bar_kfull = [&](int s) { return bar0 + 32 + 8 * s; };
   auto bar_vfull = [&](int s) { return bar0 + 48 + 8 * s; };
   auto bar_kvempty = [&](int s) { return bar0 + 64 + 8 * s; };
-  const uint32_t bar_rel = bar0 + 80, bar_tfull = bar0 + 88, bar_tread = bar0 + 96;
+  const uint32_t bar_rel = bar0 + 80, bar_tfull = bar0 + 88, bar_tread = bar0 + 96, bar_bready = bar0 + 104;
   auto bar_sfull = [&](int s) { return bar0 + 112 + 8 * s; };
   auto bar_ofull = [&](int s) { return bar0 + 128 + 8 * s; };
   auto bar_oread = [&](int s) { return bar0 + 144 + 8 * s; };
   auto bar_pready = [&](int s) { return bar0 + 160 + 8 * s; };
-  auto bar_bready = [&](int s) { return bar0 + 176 + 8 * s; };
+  const uint32_t bar_bfree = bar0 + 176;
   const uint32_t tmem_slot = bar0 + 200;
   volatile uint32_t* tmem_slot_ptr = reinterpret_cast<volatile uint32_t*>(smem_gen + L::OFF_BAR + 200);
 
@@ -87,9 +92,9 @@ attn_window4_kernel(const __grid_constant__ CUtensorMap tq64, const __grid_const
     for (int s = 0; s < 2; ++s) {
       mbar_init(bar_qfull(s), 1); mbar_init(bar_qempty(s), 1); mbar_init(bar_kfull(s), 1); mbar_init(bar_vfull(s), 1);
       mbar_init(bar_kvempty(s), 1); mbar_init(bar_sfull(s), 1); mbar_init(bar_ofull(s), 1);
-      mbar_init(bar_oread(s), 4); mbar_init(bar_pready(s), 4); mbar_init(bar_bready(s), 4);
+      mbar_init(bar_oread(s), 4); mbar_init(bar_pready(s), 4);
     }
-    mbar_init(bar_rel, 1); mbar_init(bar_tfull, 1); mbar_init(bar_tread, 4);
+    mbar_init(bar_rel, 1); mbar_init(bar_tfull, 1); mbar_init(bar_tread, 4); mbar_init(bar_bready, 4); mbar_init(bar_bfree, 1);
     fence_mbar_init();
   }
   if (warp == 17) {
@@ -101,6 +106,20 @@ attn_window4_kernel(const __grid_constant__ CUtensorMap tq64, const __grid_const
     tmem_alloc<1>(tmem_slot, 512);
     tmem_relinquish<1>();
   }
+  // The selection matrix E (bf16, the B operand of the bias MMA: 208 key rows x 64, K-major, 128-byte swizzle):
+  // E[key][c] = 1 for c = kh, 14 + kh (high and low half of bias_h[kh]) and c = 28 + kw, 42 + kw (bias_w[kw]), key = 14 kh + kw.
+  for (int i = tid; i < L::ET / 16; i += L::THREADS)
+    reinterpret_cast<uint4*>(smem_gen + L::OFF_E)[i] = make_uint4(0u, 0u, 0u, 0u);
+  __syncthreads();
+  for (int i = tid; i < 196 * 4; i += L::THREADS) {
+    const int key = i >> 2, which = i & 3;
+    const int kh = key / 14, kw = key - 14 * kh;
+    const int c = which == 0 ? kh : which == 1 ? 14 + kh : which == 2 ? 28 + kw : 42 + kw;
+    const uint32_t off = (uint32_t)(key >> 3) * 1024u + (uint32_t)(key & 7) * 128u + ((((uint32_t)c >> 3) ^ (uint32_t)(key & 7)) << 4) +
+                         (uint32_t)(c & 7) * 2u;
+    *reinterpret_cast<uint16_t*>(smem_gen + L::OFF_E + off) = 0x3F80;  // bf16 1.0
+  }
+  fence_proxy_async_smem();  // generic writes of E -> read by tcgen05.mma (async proxy)
   tc_fence_before();
   __syncthreads();
   tc_fence_after();
@@ -117,6 +136,10 @@ attn_window4_kernel(const __grid_constant__ CUtensorMap tq64, const __grid_const
   };
   // rows of the window handled by TMEM lane quarter wq of item n (row-major 14x14; rows >= 196 are not tokens)
   auto quarter_live = [](int n, int wq) { return (n & 1) * 128 + wq * 32 < 196; };
+  // debug trace of CTA 0 (AttnArgs::trace): event e of item n <- clock64()
+  auto trace = [&](int n, int e) {
+    if (a.trace != nullptr && blockIdx.x == 0) a.trace[n * 16 + e] = clock64();
+  };
 
   if (warp == 17) {
     // ------------------------------------------------------------------------------------------ TMA producer
@@ -148,10 +171,12 @@ attn_window4_kernel(const __grid_constant__ CUtensorMap tq64, const __grid_const
       }
     }
     __syncwarp();
-  } else if (warp == 16) {
-    // ------------------------------------------------------------------------------------------ MMA issuer
+  } else if (warp == 18) {
+    // ------------------------------------------------------------------------------------------ MMA issuer 2: O(n) = P V
+    // (Issuing a tcgen05.mma costs the issuing thread ~50 cycles of descriptor moves into uniform registers; at 40 MMAs
+    // per item one thread was the bottleneck of the whole pipeline, tools/window_trace.py.  PV is 26 of the 40.)
     if (elect_one()) {
-      auto issue_pv_item = [&](int m) {
+      for (int m = 0; m < N; ++m) {
         const int jm = m >> 1, g = m & 1, ksm = jm & 1;
         mbar_wait(bar_pready(g), (uint32_t)(jm & 1));
         if (g == 0) mbar_wait(bar_vfull(ksm), (uint32_t)((jm >> 1) & 1));
@@ -159,25 +184,52 @@ attn_window4_kernel(const __grid_constant__ CUtensorMap tq64, const __grid_const
         const uint32_t sbase = tmem_base + S_STRIDE * (uint32_t)g;
         issue_pv<HD, 13>(sbase + O_COL, sbase, v64(ksm), v64(ksm) + 208 * 128, false);
         umma_commit<1>(bar_ofull(g));
-        if (g == 1) umma_commit<1>(bar_kvempty(ksm));  // K and V of the pair are free once its last PV has retired
-      };
-      mbar_wait(bar_rel, 0);
-      for (int n = 0; n < N; ++n) {
-        const int j = n >> 1, g = n & 1, ks = j & 1;
-        mbar_wait(bar_qfull(g), (uint32_t)(j & 1));
-        if (n > 0) mbar_wait(bar_tread, (uint32_t)((n - 1) & 1));  // T(n-1) has been read out of the T columns
+        if (g == 1) umma_commit<1>(bar_kvempty(ksm));  // V (and K: its S MMAs retired long ago) of the pair are free
+        trace(m, 2);
+      }
+    }
+    __syncwarp();
+  } else if (warp == 16) {
+    // ------------------------------------------------------------------------------------------ MMA issuer 1: T and S
+    if (elect_one()) {
+      auto issue_t = [&](int n) {  // T(n) = Q(n) REL^T; the T columns are free once the bias warps have read T(n-1)
+        const int g = n & 1;
         tc_fence_after();
         issue_qk<HD>(tmem_base + T_COL, q64(g), q64(g) + 128 * 128, r64, r16, IDESC_T);
         umma_commit<1>(bar_tfull);
-        if (g == 0) mbar_wait(bar_kfull(ks), (uint32_t)((j >> 1) & 1));
-        if (n >= 2) mbar_wait(bar_oread(g), (uint32_t)((j - 1) & 1));  // O(n-2) has been read out of this S buffer
+        trace(n, 0);
+      };
+      auto ready_t = [&](int n) {
+        return mbar_test(bar_qfull(n & 1), (uint32_t)((n >> 1) & 1)) && (n == 0 || mbar_test(bar_tread, (uint32_t)((n - 1) & 1)));
+      };
+      auto ready_s = [&](int n) {
+        const int j = n >> 1, g = n & 1;
+        return mbar_test(bar_qfull(g), (uint32_t)(j & 1)) && mbar_test(bar_kfull(j & 1), (uint32_t)((j >> 1) & 1)) &&
+               (n < 2 || mbar_test(bar_oread(g), (uint32_t)((j - 1) & 1))) && mbar_test(bar_bready, (uint32_t)(n & 1));
+      };
+      auto issue_s = [&](int n) {
+        const int j = n >> 1, g = n & 1, ks = j & 1;
         tc_fence_after();
-        issue_qk<HD>(tmem_base + S_STRIDE * (uint32_t)g, q64(g), q64(g) + 128 * 128, k64(ks), k64(ks) + 208 * 128, IDESC_S);
+        const uint32_t s_tmem = tmem_base + S_STRIDE * (uint32_t)g;
+        issue_qk<HD>(s_tmem, q64(g), q64(g) + 128 * 128, k64(ks), k64(ks) + 208 * 128, IDESC_S);
+        umma_commit<1>(bar_qempty(g));  // (T(n), the other reader of this Q slot, was issued earlier by this thread)
+        // += [bias_h | bias_w] E^T: the bias terms (bf16 high + low halves, written into TMEM by the bias warps) times the
+        // 0/1 selection matrix -> every logit gets bias_h[kh] + bias_w[kw] in fp32 on the tensor cores
+        const uint64_t ed = make_kmajor_sw128_desc(e64);
+#pragma unroll
+        for (int k = 0; k < 4; ++k) umma_ts(s_tmem, tmem_base + B_COL + 8u * k, ed + 2u * k, IDESC_S, 1u);
         umma_commit<1>(bar_sfull(g));
-        umma_commit<1>(bar_qempty(g));
-        if (n > 0) issue_pv_item(n - 1);
+        umma_commit<1>(bar_bfree);
+        trace(n, 1);
+      };
+      mbar_wait(bar_rel, 0);
+      // Two streams with their own preconditions: S(s) (needs its bias operand and its S buffer back from the epilogue
+      // warps) and T(t), which runs up to two items ahead so that the bias gather is off the critical path.
+      int t = 0, sN = 0;
+      while (sN < N) {
+        if (sN < t && ready_s(sN)) { issue_s(sN); ++sN; continue; }
+        if (t < N && t <= sN + 1 && ready_t(t)) { issue_t(t); ++t; continue; }
       }
-      if (N > 0) issue_pv_item(N - 1);
     }
     __syncwarp();
   } else if (warp >= 12) {
@@ -192,6 +244,7 @@ attn_window4_kernel(const __grid_constant__ CUtensorMap tq64, const __grid_const
       mbar_wait(bar_pready(g), (uint32_t)((n >> 1) & 1));  // the row sums of item n are in shared memory
       mbar_wait(bar_ofull(g), (uint32_t)((n >> 1) & 1));
       tc_fence_after();
+      if (warp == 12 && lane == 0) trace(n, 8);
       if (quarter_live(n, wq)) {
         const int r = g * 128 + row;
         const bool is_tok = r < 196;
@@ -201,22 +254,60 @@ attn_window4_kernel(const __grid_constant__ CUtensorMap tq64, const __grid_const
         const bool valid = is_tok && y < 64 && x < 64;  // window_unpartition drops the padded rows / columns (:287-288)
         const size_t tok = (size_t)b * 4096 + (size_t)(valid ? y * 64 + x : 0);
         const float inv = 1.f / lsum_sm[g * 128 + row];
-        store_o_row<HD>(lane_base + S_STRIDE * (uint32_t)g + O_COL, inv, a.out + tok * a.D + head * HD, valid);
+        // O is read into registers in one go and the S buffer handed back BEFORE the row is scaled and stored
+        uint32_t o0[32], o1[32], o2[16];
+        const uint32_t o_taddr = lane_base + S_STRIDE * (uint32_t)g + O_COL;
+        tmem_ld_32x32(o_taddr, o0);
+        tmem_ld_32x32(o_taddr + 32, o1);
+        if constexpr (HD == 80) tmem_ld_32x16(o_taddr + 64, o2);
+        tmem_ld_wait();
+        tc_fence_before();
+        __syncwarp();
+        if (lane == 0) mbar_arrive(bar_oread(g));
+        if (warp == 12 && lane == 0) trace(n, 9);
+        if (valid) {
+          __nv_bfloat16* dst = a.out + tok * a.D + head * HD;
+#pragma unroll
+          for (int c = 0; c < 2; ++c) {
+            const uint32_t (&o)[32] = c ? o1 : o0;
+#pragma unroll
+            for (int h = 0; h < 2; ++h) {
+              uint32_t pk[8];
+#pragma unroll
+              for (int j = 0; j < 8; ++j)
+                pk[j] = pack_bf16x2(__uint_as_float(o[h * 16 + 2 * j]) * inv, __uint_as_float(o[h * 16 + 2 * j + 1]) * inv);
+              st_global_v8(dst + c * 32 + h * 16, pk);
+            }
+          }
+          if constexpr (HD == 80) {
+            uint32_t pk[8];
+#pragma unroll
+            for (int j = 0; j < 8; ++j) pk[j] = pack_bf16x2(__uint_as_float(o2[2 * j]) * inv, __uint_as_float(o2[2 * j + 1]) * inv);
+            st_global_v8(dst + 64, pk);
+          }
+        }
+      } else {
+        tc_fence_before();
+        __syncwarp();
+        if (lane == 0) mbar_arrive(bar_oread(g));
       }
-      tc_fence_before();
-      __syncwarp();
-      if (lane == 0) mbar_arrive(bar_oread(g));
     }
   } else if (warp >= 8) {
-    // ------------------------------------------------------------------------------------------ bias warps: T -> rel-pos terms
+    // ------------------------------------------------------------------------------------------ bias warps: T -> bias operand
     const int wq = warp & 3;
     const int row = wq * 32 + lane;
     const uint32_t lane_base = tmem_base + ((uint32_t)(wq * 32) << 16);
+    const float to_s = kLog2e / a.c1;  // bias (natural units) -> units of q . k, so that x = c1 * (q . k + bias')
     for (int n = 0; n < N; ++n) {
       const int g = n & 1;
+      const bool live = quarter_live(n, wq);
+      uint32_t pk[32];
+#pragma unroll
+      for (int i = 0; i < 32; ++i) pk[i] = 0u;
       mbar_wait(bar_tfull, (uint32_t)(n & 1));
       tc_fence_after();
-      if (quarter_live(n, wq)) {
+      if (warp == 8 && lane == 0) trace(n, 3);
+      if (live) {
         const int r = g * 128 + row;
         const bool is_tok = r < 196;
         const int qh = is_tok ? r / 14 : 0, qw = is_tok ? r % 14 : 0;
@@ -229,46 +320,55 @@ attn_window4_kernel(const __grid_constant__ CUtensorMap tq64, const __grid_const
         for (int i = 0; i < 64; ++i) tl[i] = __uint_as_float(v[i]);
         const float* th = tl + qh + 13;       // q . rel_pos_h[qh - kh + 13]
         const float* tw = tl + 32 + qw + 13;  // q . rel_pos_w[qw - kw + 13]
-        float* dst = bias_sm + (size_t)(g * 128 + row) * L::BIAS_PITCH;
+        // operand columns (two bf16 each): K index 0..13 bias_h high halves, 14..27 low halves, 28..41 bias_w high, 42..55 low
+        float hi[28], lo[28];
 #pragma unroll
         for (int k = 0; k < 14; ++k) {
-          dst[k] = th[-k] * kLog2e;
-          dst[14 + k] = tw[-k] * kLog2e;
+          const float bh = th[-k] * to_s, bw = tw[-k] * to_s;
+          hi[k] = __bfloat162float(__float2bfloat16_rn(bh));
+          lo[k] = bh - hi[k];
+          hi[14 + k] = __bfloat162float(__float2bfloat16_rn(bw));
+          lo[14 + k] = bw - hi[14 + k];
+        }
+#pragma unroll
+        for (int k = 0; k < 7; ++k) {
+          pk[k] = pack_bf16x2(hi[2 * k], hi[2 * k + 1]);
+          pk[7 + k] = pack_bf16x2(lo[2 * k], lo[2 * k + 1]);
+          pk[14 + k] = pack_bf16x2(hi[14 + 2 * k], hi[15 + 2 * k]);
+          pk[21 + k] = pack_bf16x2(lo[14 + 2 * k], lo[15 + 2 * k]);
         }
       }
       tc_fence_before();
       __syncwarp();
-      if (lane == 0) {
-        mbar_arrive(bar_tread);
-        mbar_arrive(bar_bready(g));
+      if (lane == 0) mbar_arrive(bar_tread);  // T(n) is in registers: the issuer may overwrite the T columns
+      if (warp == 8 && lane == 0) trace(n, 4);
+      if (n > 0) {
+        mbar_wait(bar_bfree, (uint32_t)((n - 1) & 1));  // the bias MMA of item n-1 has read the operand columns
+        tc_fence_after();
       }
+      tmem_st_32x32(lane_base + B_COL, pk);  // dead quarters store zeros (their rows are never read back)
+      tmem_st_wait();
+      tc_fence_before();
+      __syncwarp();
+      if (lane == 0) mbar_arrive(bar_bready);
+      if (warp == 8 && lane == 0) trace(n, 5);
     }
   } else {
     // ------------------------------------------------------------------------------------------ softmax groups
     const int g = warp >> 2, wq = warp & 3;
     const int row = wq * 32 + lane;  // row of the 128-row tile == TMEM lane
     const uint32_t sbase = tmem_base + ((uint32_t)(wq * 32) << 16) + S_STRIDE * (uint32_t)g;
-    const uint64_t c12 = f2_pack(a.c1, a.c1);
+    const float c1 = a.c1;
+    const uint64_t c12 = f2_pack(c1, c1);
     const bool live = quarter_live(g, wq);  // group g always works on items with mt == g
     for (int n = g; n < N; n += 2) {
-      const uint32_t ph = (uint32_t)((n >> 1) & 1);
-      uint64_t bH2[14], bW2[7];
-      mbar_wait(bar_bready(g), ph);
-      if (live) {
-        const float* src = bias_sm + (size_t)(g * 128 + row) * L::BIAS_PITCH;
-#pragma unroll
-        for (int k = 0; k < 14; ++k) bH2[k] = f2_pack(src[k], src[k]);
-#pragma unroll
-        for (int k = 0; k < 7; ++k) bW2[k] = f2_pack(src[14 + 2 * k], src[15 + 2 * k]);
-      }
-      mbar_wait(bar_sfull(g), ph);
+      mbar_wait(bar_sfull(g), (uint32_t)((n >> 1) & 1));
       tc_fence_after();
+      if (wq == 0 && lane == 0) trace(n, 6);
       float lsum = 1.f;
       if (live) {
-        // x(j) = s(j) * scale * log2e + bias_h[j / 14] + bias_w[j % 14], two keys per instruction (j even: same key row)
-#define INKSAM_WIN_X2(v, j, i) \
-  f2_fma(f2_pack(__uint_as_float((v)[i]), __uint_as_float((v)[(i) + 1])), c12, f2_add(bH2[(j) / 14], bW2[((j) % 14) / 2]))
-        // ---- pass 1: the row maximum over the 196 keys (keys 196..207 of the box belong to the next window)
+        // S already holds q . k + bias / scale.  Pass 1: the TRUE row maximum over the 196 keys (columns 196..207 of the
+        // box belong to the next window), as in the reference softmax: exact for any logit range, nothing is clamped.
         float m = -INFINITY;
         {
           uint32_t va[32], vb[32];
@@ -280,17 +380,14 @@ attn_window4_kernel(const __grid_constant__ CUtensorMap tq64, const __grid_const
             tmem_ld_wait();
             if (c < 6) tmem_ld_32x32(sbase + (c + 1) * 32, nxt);  // chunk 6: columns 192..223, only 192..195 are keys
 #pragma unroll
-            for (int i = 0; i < (c < 6 ? 32 : 4); i += 2) {
-              float x0, x1;
-              f2_unpack(INKSAM_WIN_X2(cur, c * 32 + i, i), x0, x1);
-              m = fmaxf(m, fmaxf(x0, x1));
-            }
+            for (int i = 0; i < (c < 6 ? 32 : 4); i += 2)
+              m = fmaxf(m, fmaxf(__uint_as_float(cur[i]), __uint_as_float(cur[i + 1])));
           }
         }
-        // ---- pass 2: p = exp2(x - max), P (bf16) over S, row sum
-        const uint64_t nm2 = f2_pack(-m, -m);
-#pragma unroll
-        for (int k = 0; k < 14; ++k) bH2[k] = f2_add(bH2[k], nm2);  // fold the shift into the row bias
+        // Pass 2: p = exp2(c1 * (s - max)), P (bf16) over the first 104 columns of S, row sum
+        if (wq == 0 && lane == 0) trace(n, 7);
+        const float nm = -m * c1;
+        const uint64_t nm2 = f2_pack(nm, nm);
         uint64_t l2 = f2_pack(0.f, 0.f);
         {
           uint32_t va[32], vb[32];
@@ -306,7 +403,7 @@ attn_window4_kernel(const __grid_constant__ CUtensorMap tq64, const __grid_const
             for (int i = 0; i < 32; i += 2) {
               if (i < (c < 6 ? 32 : 4)) {
                 float x0, x1, p0, p1;
-                f2_unpack(INKSAM_WIN_X2(cur, c * 32 + i, i), x0, x1);
+                f2_unpack(f2_fma(f2_pack(__uint_as_float(cur[i]), __uint_as_float(cur[i + 1])), c12, nm2), x0, x1);
                 if (i >= 32 - KPOLY && c < 6) {
                   f2_unpack(f2_exp2_poly(f2_pack(fmaxf(x0, -126.f), fmaxf(x1, -126.f))), p0, p1);
                 } else {
@@ -323,7 +420,6 @@ attn_window4_kernel(const __grid_constant__ CUtensorMap tq64, const __grid_const
             else tmem_st_32x8(sbase + 96, *reinterpret_cast<uint32_t(*)[8]>(&pk[0]));  // keys 192..207: 4 real, 12 zero
           }
         }
-#undef INKSAM_WIN_X2
         tmem_st_wait();
         float la, lb;
         f2_unpack(l2, la, lb);
@@ -333,6 +429,7 @@ attn_window4_kernel(const __grid_constant__ CUtensorMap tq64, const __grid_const
       tc_fence_before();
       __syncwarp();
       if (lane == 0) mbar_arrive(bar_pready(g));
+      if (wq == 0 && lane == 0) trace(n, 10);
       // S buffer g is rewritten by S(n+2) only after the epilogue warps have read O(n) (bar_oread): nothing to wait for here
     }
   }

@@ -52,6 +52,7 @@ int launch_gemm(int cg, int tf32, int bn, int epi, const void* A, int lda, const
 
 int launch_attention(int windowed, const void* qkv, const void* rel, void* out, int B, int heads, int head_dim,
                      cudaStream_t st);
+void set_attention_trace(long long* buf);
 int launch_patchify(const void* images, int dtype, int B, const int* hw, long long img_stride, long long row_pitch,
                     long long plane_stride, const float* mean, const float* stdv, void* out, cudaStream_t st);
 int launch_layernorm_bf16(const float* x, const float* w, const float* b, void* out, int M, int D, float eps, int plain,

@@ -207,6 +207,14 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
           if (++stage == C::STAGES) { stage = 0; phase ^= 1u; }
         }
       }
+      // Teardown: the last STAGES tcgen05.commit arrivals on this CTA's empty barriers (for a CTA pair: multicast from the
+      // leader's MMA thread, possibly in the other SM) have not been waited for by anyone.  Walk the ring once more without
+      // loading: when this returns every commit-armed arrival has landed in this CTA's shared memory, so nothing can
+      // arrive after the CTA has exited and its shared memory has been handed to the next CTA.
+      for (int i = 0; i < C::STAGES; ++i) {
+        mbar_wait(empty_bar(stage), phase ^ 1u);
+        if (++stage == C::STAGES) { stage = 0; phase ^= 1u; }
+      }
     }
     __syncwarp();
   } else if (warp == 1) {

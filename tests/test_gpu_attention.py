@@ -81,7 +81,7 @@ def test_global_attention_late_peak_rescales(hd, peak_at, gain):
     assert rel_err(out, ref) < 1.5e-2
 
 
-@pytest.fixture(params=["v4", "v4-kpoly8", "v3", "v2"])
+@pytest.fixture(params=["v5", "v5-kpoly8", "v4", "v3", "v2"])
 def window_kernel(request, monkeypatch):
     """The windowed kernel variants (read per launch by attn_host.cu): the current one with its default / no / double
     share of polynomial exp2, and the previous kernel as a cross-check."""
@@ -121,12 +121,13 @@ def test_window_attention(hd, heads, B, window_kernel):
 
 
 @pytest.mark.parametrize("hd,peak_key,gain", [(80, 150, 170.0), (64, 195, 400.0), (80, 40, 50.0), (64, 97, 170.0), (80, 98, 400.0)])
-def test_window_attention_late_peak(hd, peak_key, gain, monkeypatch):
+@pytest.mark.parametrize("version", ["4", "5"])
+def test_window_attention_late_peak(hd, peak_key, gain, version, monkeypatch):
     """Windowed blocks with two keys of every window far above the others (beyond the first 32 keys and, for gain >= 170,
     more than 120 log2 units above them, 7 log2 units apart): the softmax must stay exact -- the reference subtracts the
     true row maximum.  (A kernel that clamps the exponent gives both keys the same weight and fails this.)"""
     lib = _lib.load()
-    monkeypatch.setenv("INKSAM_WINDOW_ATTN", "4")
+    monkeypatch.setenv("INKSAM_WINDOW_ATTN", version)
     heads, B = 2, 1
     g = torch.Generator().manual_seed(300 + hd + peak_key)
     D = heads * hd

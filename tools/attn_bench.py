@@ -43,8 +43,12 @@ for (B, heads, hd) in [(8, 16, 80), (1, 16, 80), (8, 12, 64)]:
     os.environ.pop("INKSAM_GLOBAL_KPOLY", None)
     ref = None
     for name, env in [("v2", {"INKSAM_WINDOW_ATTN": "2"}),
-                      ("v3", {"INKSAM_WINDOW_ATTN": "3"}),
-                      ("v4 kpoly 0", {"INKSAM_WINDOW_ATTN": "4"}), ("v4 kpoly 8", {"INKSAM_WINDOW_ATTN": "4", "INKSAM_WINDOW_KPOLY": "8"})]:
+                      
+                      ("v4", {"INKSAM_WINDOW_ATTN": "4"}), ("v5 kpoly 0", {"INKSAM_WINDOW_ATTN": "5", "INKSAM_WINDOW_KPOLY": "0"}),
+                      ("v5 kpoly 4", {"INKSAM_WINDOW_ATTN": "5", "INKSAM_WINDOW_KPOLY": "4"}),
+                      ("v5 kpoly 8", {"INKSAM_WINDOW_ATTN": "5", "INKSAM_WINDOW_KPOLY": "8"}),
+                      ("v5 kpoly 12", {"INKSAM_WINDOW_ATTN": "5", "INKSAM_WINDOW_KPOLY": "12"}),
+                      ("v5 kpoly 16", {"INKSAM_WINDOW_ATTN": "5", "INKSAM_WINDOW_KPOLY": "16"})]:
         for k in ("INKSAM_WINDOW_ATTN", "INKSAM_WINDOW_KPOLY"):
             os.environ.pop(k, None)
         os.environ.update(env)
