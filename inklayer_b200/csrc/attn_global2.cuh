@@ -115,9 +115,21 @@ attn_global2_kernel(const __grid_constant__ CUtensorMap tm64, const __grid_const
       mbar_arrive_expect_tx(bar_rel, 2 * TILE_TX);
       load_tile(k_tile(0), &tr64, &tr16, bar_rel, 0, 0);     // rel_pos_h rows
       load_tile(k_tile(1), &tr64, &tr16, bar_rel, 0, 128);   // rel_pos_w rows
+      // V (HD == 80): FIVE [128 keys][16 columns] tiles with 32-byte rows / 32-byte swizzle, 4096 bytes apart = one MN-major
+      // operand of N = 80, so that P V takes ONE tcgen05.mma per 16 keys instead of a 64-column and a 16-column one: the
+      // tensor pipe spends >= 46 cycles on an MMA however small it is (tools/micro/mma_issue.cu), and with 13 MMAs per
+      // 64-key sub-tile and group that issue cost, not the MUFU pipe, bounded this kernel.
+      auto load_v = [&](uint32_t dst, uint32_t bar, int row) {
+        if constexpr (HD == 80) {
+#pragma unroll
+          for (int t = 0; t < 5; ++t) tma_load_2d(dst + t * 4096, &tm16, bar, col_v + 16 * t, row);
+        } else {
+          tma_load_2d(dst, &tm64, bar, col_v, row);
+        }
+      };
       for (int s = 0; s < 2; ++s) {
         mbar_arrive_expect_tx(bar_vfull(s), TILE_TX);
-        load_tile(v_tile(s), &tm64, &tm16, bar_vfull(s), col_v, b * 4096 + s * 128);
+        load_v(v_tile(s), bar_vfull(s), b * 4096 + s * 128);
       }
       mbar_wait(bar_tdone, 0);  // the T MMAs have read the rel tables: the K ring is free
       for (int j = 0; j < NT; ++j) {
@@ -129,7 +141,7 @@ attn_global2_kernel(const __grid_constant__ CUtensorMap tm64, const __grid_const
         if (j >= 2) {
           mbar_wait(bar_vempty(s), par);
           mbar_arrive_expect_tx(bar_vfull(s), TILE_TX);
-          load_tile(v_tile(s), &tm64, &tm16, bar_vfull(s), col_v, b * 4096 + j * 128);
+          load_v(v_tile(s), bar_vfull(s), b * 4096 + j * 128);
         }
       }
     }
@@ -170,8 +182,20 @@ attn_global2_kernel(const __grid_constant__ CUtensorMap tm64, const __grid_const
         mbar_wait(bar_pready(g, buf), par);
         tc_fence_after();
         const uint32_t vt = v_tile(vs);
-        issue_pv<HD, 4>(tmem_base + O_COL(g), tmem_base + S_COL(g, buf), vt + buf * 64 * 128, vt + 128 * 128 + buf * 64 * 32,
-                        t != 0);
+        if constexpr (HD == 80) {
+          // MN-major B operand, 32-byte swizzle: five 16-column atoms along N (leading byte offset 4096), 8-key groups 256
+          // bytes apart along K; the sub-tile's 64 keys start 64 * 32 bytes into the tile; 16 keys per MMA = 512 bytes
+          constexpr uint32_t ID80 = make_idesc_bmn(1u, 128, 80);
+          uint64_t vd = make_sw32_desc(vt + buf * 64 * 32);
+          vd = (vd & ~(uint64_t)0x3FFF0000ull) | ((uint64_t)(4096 >> 4) << 16);
+#pragma unroll
+          for (int ks = 0; ks < 4; ++ks)
+            umma_ts(tmem_base + O_COL(g), tmem_base + S_COL(g, buf) + 8u * ks, vd + (uint64_t)(ks * (16 * 32 / 16)), ID80,
+                    (uint32_t)(t != 0 || ks != 0));
+        } else {
+          issue_pv<HD, 4>(tmem_base + O_COL(g), tmem_base + S_COL(g, buf), vt + buf * 64 * 128, vt + 128 * 128 + buf * 64 * 32,
+                          t != 0);
+        }
         umma_commit<1>(bar_pvdone(g, buf));
         if (t + 2 < NS) {
           issue_s(t + 2);  // executes after the PV above (in order), the last reader of P(t) in this S buffer

@@ -17,6 +17,8 @@ class SamPredictor:
     def __init__(self, sam_model: Sam) -> None:
         self.model = sam_model
         self.transform = ResizeLongestSide(sam_model.image_encoder.img_size)
+        self._stage_u8 = None    # device staging buffers in the input frame: a stable pointer for the encoder's CUDA graph
+        self._stage_f32 = None
         self.reset_image()
 
     @property
@@ -53,10 +55,26 @@ class SamPredictor:
         self._encode(t, tuple(original_image_size), tuple(transformed_image.shape[-2:]))
 
     def _encode(self, t: torch.Tensor, original_size, input_size) -> None:
+        """One image through the encoder.  The image is copied into a per-predictor staging buffer of the model's input
+        frame so that the ~200 kernel launches of the batch-1 encode replay from a CUDA graph (captured per input size the
+        second time it is seen): `set_image` on a stream of sketches is launch-bound otherwise.  The embedding is copied out
+        of the graph's buffer: `features` stays valid until reset_image / the next set_image, as in the reference."""
         self.reset_image()
+        S = self.model.image_encoder.img_size
+        h, w = int(input_size[0]), int(input_size[1])
+        if t.dtype == torch.uint8:
+            if self._stage_u8 is None:
+                self._stage_u8 = torch.zeros((1, S, S, 3), dtype=torch.uint8, device=self.device)
+            self._stage_u8[0, :h, :w].copy_(t[0])
+            feats = self.model.encode(self._stage_u8, [(h, w)], graph=True)
+        else:
+            if self._stage_f32 is None:
+                self._stage_f32 = torch.zeros((1, 3, S, S), dtype=torch.float32, device=self.device)
+            self._stage_f32[0, :, :h, :w].copy_(t[0])
+            feats = self.model.encode(self._stage_f32, [(h, w)], graph=True)
         self.original_size = original_size
         self.input_size = input_size
-        self.features = self.model.encode(t)
+        self.features = feats.clone()
         self.is_image_set = True
 
     def get_image_embedding(self) -> torch.Tensor:
