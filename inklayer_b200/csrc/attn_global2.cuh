@@ -66,6 +66,7 @@ attn_global2_kernel(const __grid_constant__ CUtensorMap tm64, const __grid_const
   auto bar_pready = [&](int g, int buf) { return bar0 + 128 + 8 * (2 * g + buf); };
   auto bar_pvdone = [&](int g, int buf) { return bar0 + 160 + 8 * (2 * g + buf); };
   const uint32_t tmem_slot = bar0 + 192;
+  auto bar_done = [&](int g) { return bar0 + 200 + 8 * g; };  // teardown: an issuer's last commit-armed arrivals have landed
   volatile uint32_t* tmem_slot_ptr = reinterpret_cast<volatile uint32_t*>(smem_gen + L::OFF_BAR + 192);
 
   const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
@@ -77,6 +78,7 @@ attn_global2_kernel(const __grid_constant__ CUtensorMap tm64, const __grid_const
 
   if (tid == 0) {
     mbar_init(bar_q, 1); mbar_init(bar_rel, 1); mbar_init(bar_tdone, 2); mbar_init(bar_tread, 8);
+    mbar_init(bar_done(0), 1); mbar_init(bar_done(1), 1);
     for (int s = 0; s < 2; ++s) {
       mbar_init(bar_kfull(s), 1); mbar_init(bar_kempty(s), 2); mbar_init(bar_vfull(s), 1); mbar_init(bar_vempty(s), 2);
       for (int buf = 0; buf < 2; ++buf) {
@@ -206,6 +208,10 @@ attn_global2_kernel(const __grid_constant__ CUtensorMap tm64, const __grid_const
           if (j + 1 < NT) umma_commit<1>(bar_kempty((j + 1) & 1));
         }
       }
+      // Teardown: nobody waits for this thread's last v_empty / k_empty arrivals.  One more commit, waited for here: when it
+      // has landed, every earlier commit-armed arrival of this thread has landed too.
+      umma_commit<1>(bar_done(g));
+      mbar_wait(bar_done(g), 0);
     }
     __syncwarp();
   } else {

@@ -71,6 +71,7 @@ attn_window5_kernel(const __grid_constant__ CUtensorMap tq64, const __grid_const
   auto bar_oread = [&](int s) { return bar0 + 144 + 8 * s; };
   auto bar_pready = [&](int s) { return bar0 + 160 + 8 * s; };
   const uint32_t bar_bfree = bar0 + 176;
+  auto bar_done = [&](int i) { return bar0 + 184 + 8 * i; };  // teardown: the issuers' last commit-armed arrivals have landed
   const uint32_t tmem_slot = bar0 + 200;
   volatile uint32_t* tmem_slot_ptr = reinterpret_cast<volatile uint32_t*>(smem_gen + L::OFF_BAR + 200);
 
@@ -82,6 +83,7 @@ attn_window5_kernel(const __grid_constant__ CUtensorMap tq64, const __grid_const
       mbar_init(bar_oread(s), 4); mbar_init(bar_pready(s), 8);
     }
     mbar_init(bar_rel, 1); mbar_init(bar_tfull, 1); mbar_init(bar_tread, 4); mbar_init(bar_bready, 4); mbar_init(bar_bfree, 1);
+    mbar_init(bar_done(0), 1); mbar_init(bar_done(1), 1);
     fence_mbar_init();
   }
   if (warp == 17) {
@@ -199,6 +201,11 @@ attn_window5_kernel(const __grid_constant__ CUtensorMap tq64, const __grid_const
         if (g == 1) umma_commit<1>(bar_kvempty(ksm));  // V (and K: its S MMAs retired long ago) of the pair are free
         trace(m, 2);
       }
+      // Teardown: nobody waits for this thread's last kv_empty arrival.  One more commit, waited for here: when it has
+      // landed every earlier commit-armed arrival of this thread has landed too, so none can hit shared memory that
+      // already belongs to the next CTA.
+      umma_commit<1>(bar_done(1));
+      mbar_wait(bar_done(1), 0);
     }
     __syncwarp();
   } else if (warp == 16) {
@@ -242,6 +249,8 @@ attn_window5_kernel(const __grid_constant__ CUtensorMap tq64, const __grid_const
         if (sN < t && ready_s(sN)) { issue_s(sN); ++sN; continue; }
         if (t < N && t <= sN + 1 && ready_t(t)) { issue_t(t); ++t; continue; }
       }
+      umma_commit<1>(bar_done(0));  // teardown: the last q_empty / b_free arrivals (see issuer 2)
+      mbar_wait(bar_done(0), 0);
     }
     __syncwarp();
   } else if (warp >= 12) {

@@ -14,6 +14,20 @@ def main():
     top_n = int(sys.argv[2]) if len(sys.argv) > 2 else 25
     out = subprocess.run(["ncu", "-i", path, "--page", "source", "--csv", "--print-source", "sass"], capture_output=True, text=True).stdout
     rows = list(csv.reader(io.StringIO(out)))
+    # one section per profiled launch: a "Kernel Name" row, a header row, then one row per SASS instruction
+    starts = [i for i, r in enumerate(rows) if r and r[0] == "Kernel Name"]
+    seen = set()
+    for k, i0 in enumerate(starts):
+        i1 = starts[k + 1] if k + 1 < len(starts) else len(rows)
+        key = (rows[i0][1], tuple(tuple(r[:4]) for r in rows[i0 + 2:i0 + 6]))  # (ncu lists every launch twice)
+        if key in seen:
+            continue
+        seen.add(key)
+        section(rows[i0:i1], top_n)
+        print()
+
+
+def section(rows, top_n):
     print("#", rows[0][1][:150])
     hdr, data = rows[1], [r for r in rows[2:] if len(r) > 5]
     isamp, ia, iex = hdr.index("# Samples"), hdr.index("Source"), hdr.index("Instructions Executed")
