@@ -15,46 +15,62 @@ constexpr int NT = 7;        // iou token + 4 mask tokens + 2 box corners
 constexpr int TOK_THREADS = 512;
 
 // out[t][n] = act(sum_k in[t][k] * W[n][k] + b[n]) for t < T; in/out in shared memory, W row-major in global.
-// One warp per output row, lanes split k (coalesced 512-byte weight reads), two rows in flight per warp.
+// One warp per group of R = 4 output rows, lanes split k (coalesced 512-byte weight reads).  The weights come from L2
+// (every CTA = box re-streams them): with one 16-byte load per row in flight the loop was bound by the L2 round trip
+// (~600 cycles, 220 us for the two MLP phases of 128 boxes), so each lane now has R x U = 8 weight loads in flight.
 template <int T>
 __device__ __forceinline__ void linear_tok(float* __restrict__ out, int out_ld, const float* __restrict__ in, int in_ld,
                                            const float* __restrict__ W, const float* __restrict__ bias, int N, int Kd,
                                            bool relu, bool accumulate) {
+  constexpr int R = 4, U = 2;
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31, nwarps = blockDim.x >> 5;
-  for (int n0 = warp * 2; n0 < N; n0 += nwarps * 2) {
-    float acc0[T], acc1[T];
+  const int k4n = Kd / 4;
+  for (int n0 = warp * R; n0 < N; n0 += nwarps * R) {
+    float acc[R][T];
 #pragma unroll
-    for (int t = 0; t < T; ++t) { acc0[t] = 0.f; acc1[t] = 0.f; }
-    const bool has1 = n0 + 1 < N;
-    const float4* w0 = reinterpret_cast<const float4*>(W + (size_t)n0 * Kd);
-    const float4* w1 = reinterpret_cast<const float4*>(W + (size_t)(has1 ? n0 + 1 : n0) * Kd);
-    for (int k4 = lane; k4 < Kd / 4; k4 += 32) {
-      const float4 a = __ldg(w0 + k4), b = __ldg(w1 + k4);
+    for (int r = 0; r < R; ++r)
 #pragma unroll
-      for (int t = 0; t < T; ++t) {
-        const float4 x = *reinterpret_cast<const float4*>(in + t * in_ld + k4 * 4);
-        acc0[t] += a.x * x.x + a.y * x.y + a.z * x.z + a.w * x.w;
-        acc1[t] += b.x * x.x + b.y * x.y + b.z * x.z + b.w * x.w;
+      for (int t = 0; t < T; ++t) acc[r][t] = 0.f;
+    const float4* w[R];
+#pragma unroll
+    for (int r = 0; r < R; ++r) w[r] = reinterpret_cast<const float4*>(W + (size_t)(n0 + r < N ? n0 + r : n0) * Kd);
+    for (int k4 = lane; k4 < k4n; k4 += 32 * U) {
+      float4 a[U][R];
+#pragma unroll
+      for (int u = 0; u < U; ++u) {
+        const int kk = k4 + 32 * u;
+#pragma unroll
+        for (int r = 0; r < R; ++r) a[u][r] = kk < k4n ? __ldg(w[r] + kk) : make_float4(0.f, 0.f, 0.f, 0.f);
+      }
+#pragma unroll
+      for (int u = 0; u < U; ++u) {
+        const int kk = k4 + 32 * u;
+        if (kk < k4n) {
+#pragma unroll
+          for (int t = 0; t < T; ++t) {
+            const float4 x = *reinterpret_cast<const float4*>(in + t * in_ld + kk * 4);
+#pragma unroll
+            for (int r = 0; r < R; ++r) acc[r][t] += a[u][r].x * x.x + a[u][r].y * x.y + a[u][r].z * x.z + a[u][r].w * x.w;
+          }
+        }
       }
     }
 #pragma unroll
-    for (int t = 0; t < T; ++t) {
+    for (int r = 0; r < R; ++r)
 #pragma unroll
-      for (int o = 16; o > 0; o >>= 1) {
-        acc0[t] += __shfl_xor_sync(0xffffffffu, acc0[t], o);
-        acc1[t] += __shfl_xor_sync(0xffffffffu, acc1[t], o);
-      }
-    }
+      for (int t = 0; t < T; ++t)
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) acc[r][t] += __shfl_xor_sync(0xffffffffu, acc[r][t], o);
     if (lane == 0) {
 #pragma unroll
-      for (int t = 0; t < T; ++t) {
-        float v0 = acc0[t] + (bias ? bias[n0] : 0.f);
-        if (relu) v0 = fmaxf(v0, 0.f);
-        if (accumulate) out[t * out_ld + n0] += v0; else out[t * out_ld + n0] = v0;
-        if (has1) {
-          float v1 = acc1[t] + (bias ? bias[n0 + 1] : 0.f);
-          if (relu) v1 = fmaxf(v1, 0.f);
-          if (accumulate) out[t * out_ld + n0 + 1] += v1; else out[t * out_ld + n0 + 1] = v1;
+      for (int r = 0; r < R; ++r) {
+        if (n0 + r < N) {
+#pragma unroll
+          for (int t = 0; t < T; ++t) {
+            float v = acc[r][t] + (bias ? bias[n0 + r] : 0.f);
+            if (relu) v = fmaxf(v, 0.f);
+            if (accumulate) out[t * out_ld + n0 + r] += v; else out[t * out_ld + n0 + r] = v;
+          }
         }
       }
     }
