@@ -30,7 +30,9 @@ struct AttnGlobal2 {
   static constexpr int OFF_K = 2 * TILE;                  // K ring, 2 slots
   static constexpr int OFF_V = 4 * TILE;                  // V ring, 2 slots
   static constexpr int OFF_BH = 6 * TILE;                 // biasH [256][66] fp32
-  static constexpr int OFF_BAR = OFF_BH + 256 * BH_PITCH * 4;
+  static constexpr int TW_PITCH = 97;                     // floats per row of a warp's T_w scratch (odd: conflict-free writes)
+  static constexpr int TW_WARP = 32 * TW_PITCH * 4;       // prologue scratch of one softmax warp; the 8 of them overlay biasH
+  static constexpr int OFF_BAR = OFF_BH + (8 * TW_WARP > 256 * BH_PITCH * 4 ? 8 * TW_WARP : 256 * BH_PITCH * 4);
   static constexpr int SMEM_BYTES = OFF_BAR + 256 + 1024;
   static constexpr int THREADS = 352;
 };
@@ -100,6 +102,13 @@ attn_global2_kernel(const __grid_constant__ CUtensorMap tm64, const __grid_const
   __syncthreads();
   tc_fence_after();
   const uint32_t tmem_base = *tmem_slot_ptr;
+  // Debug trace of CTA 0 (AttnArgs::trace, tools/global_trace.py): event e of sub-tile t <- clock64().  Compiled in with
+  // -DINKSAM_ATTN_TRACE only: even disabled at run time the hooks cost ~10 % of this kernel's time.
+  auto trace = [&](int t, int e) {
+#ifdef INKSAM_ATTN_TRACE
+    if (a.trace != nullptr && blockIdx.x == 0) a.trace[t * 16 + e] = clock64();
+#endif
+  };
   pdl_launch_dependents();  // the proj GEMM (launched with PDL) may run its prologue under this kernel's tail
   auto S_COL = [](int g, int buf) { return (uint32_t)(128 * g + 64 * buf); };
   auto O_COL = [](int g) { return (uint32_t)(256 + 128 * g); };
@@ -181,8 +190,10 @@ attn_global2_kernel(const __grid_constant__ CUtensorMap tm64, const __grid_const
           mbar_wait(bar_vfull(vs), (uint32_t)((j >> 1) & 1));
           if (j + 1 < NT) mbar_wait(bar_kfull((j + 1) & 1), (uint32_t)(((j + 1) >> 1) & 1));
         }
+        if (g == 0) trace(t, 9);
         mbar_wait(bar_pready(g, buf), par);
         tc_fence_after();
+        if (g == 0) trace(t, 10);
         const uint32_t vt = v_tile(vs);
         if constexpr (HD == 80) {
           // MN-major B operand, 32-byte swizzle: five 16-column atoms along N (leading byte offset 4096), 8-key groups 256
@@ -203,6 +214,7 @@ attn_global2_kernel(const __grid_constant__ CUtensorMap tm64, const __grid_const
           issue_s(t + 2);  // executes after the PV above (in order), the last reader of P(t) in this S buffer
           umma_commit<1>(bar_sfull(g, buf));
         }
+        if (g == 0) trace(t, 11);
         if (buf == 1) {
           umma_commit<1>(bar_vempty(vs));
           if (j + 1 < NT) umma_commit<1>(bar_kempty((j + 1) & 1));
@@ -228,23 +240,31 @@ attn_global2_kernel(const __grid_constant__ CUtensorMap tm64, const __grid_const
     tc_fence_after();
     uint64_t bW2[32];  // (bias_w[2j], bias_w[2j+1]) * log2e for this query, packed for f32x2 arithmetic
     {
-      float t[128];  // T_w row; indexed per thread below -> lives in local memory
+      // T_w[q][qw - kw + 63], kw = 0..63: a 64-column window of the thread's T_w row that starts at column qw, i.e. at a
+      // different column in every lane.  TMEM addresses are warp-uniform, so the 95 columns the warp's 32 queries need
+      // (qw = qw0 + lane) go through a shared-memory scratch: row pitch 97 floats -> the writes are conflict-free, the
+      // skewed reads 2-way.  (Round 1 did this transpose in a per-thread local array: 64 loads x 32 lines per warp, 4 %
+      // of the kernel.)  The scratch of the 8 warps overlays biasH, hence the 256-thread barrier before biasH is written.
+      float* tw = reinterpret_cast<float*>(smem_gen + L::OFF_BH + warp * L::TW_WARP) + lane * L::TW_PITCH;
+      const uint32_t qw0 = (uint32_t)(qw & 32);
       uint32_t v[32];
 #pragma unroll
-      for (int c = 0; c < 4; ++c) {
-        tmem_ld_32x32(lane_base + 256 * g + 128 + c * 32, v);
+      for (int c = 0; c < 3; ++c) {
+        tmem_ld_32x32(lane_base + 256 * g + 128 + qw0 + c * 32, v);
         tmem_ld_wait();
 #pragma unroll
-        for (int i = 0; i < 32; ++i) t[c * 32 + i] = __uint_as_float(v[i]);
+        for (int i = 0; i < 32; ++i) tw[c * 32 + i] = __uint_as_float(v[i]);
       }
-      const float* tp = t + qw + 63;
+      __syncwarp();
+      const float* tp = tw + lane + 63;  // column qw + 63 of the row
 #pragma unroll
-      for (int i = 0; i < 64; i += 2) bW2[i >> 1] = f2_pack(tp[-i] * kLog2e, tp[-i - 1] * kLog2e);  // T_w[q][qw - kw + 63]
+      for (int i = 0; i < 64; i += 2) bW2[i >> 1] = f2_pack(tp[-i] * kLog2e, tp[-i - 1] * kLog2e);
       // T_h[q][qh - kh + 63]: qh is uniform over the warp, so the 64 needed columns start at column qh for all lanes
       uint32_t h0[32], h1[32];
       tmem_ld_32x32(lane_base + 256 * g + (uint32_t)qh, h0);
       tmem_ld_32x32(lane_base + 256 * g + (uint32_t)qh + 32, h1);
       tmem_ld_wait();
+      named_bar_sync(1, 256);  // every softmax warp has read its scratch
 #pragma unroll
       for (int i = 0; i < 32; ++i) {
         bh_row[63 - i] = __uint_as_float(h0[i]) * kLog2e;
@@ -268,6 +288,7 @@ attn_global2_kernel(const __grid_constant__ CUtensorMap tm64, const __grid_const
       const float bh = bh_row[t];  // key row kh = t
       mbar_wait(bar_sfull(g, buf), par);
       tc_fence_after();
+      if (g == 0 && lane == 0) trace(t, 4 + (warp & 3));
       uint32_t v0[32], v1[32];
       tmem_ld_32x32(s_addr, v0);
       tmem_ld_32x32(s_addr + 32, v1);
@@ -374,6 +395,7 @@ attn_global2_kernel(const __grid_constant__ CUtensorMap tm64, const __grid_const
       tc_fence_before();
       __syncwarp();
       if (lane == 0) mbar_arrive(bar_pready(g, buf));
+      if (g == 0 && lane == 0) trace(t, warp & 3);
       // The running sum bounds every probability so far: once it passes 2^32 the shift moves up by log2(l) (an exact
       // power-of-two rescale of l and O), so no per-element maximum has to be tracked in the hot loop.
       const bool need = l > 4294967296.f;
