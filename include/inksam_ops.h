@@ -97,6 +97,18 @@ size_t inksam_resize_workspace_bytes(int H, int W, int out_h, int out_w);
 int inksam_resize_u8(const uint8_t* src, int H, int W, long long src_row_pitch, uint8_t* dst, int out_h, int out_w,
                      long long dst_row_pitch, void* workspace, void* stream);
 
+/* inksam_resize_u8 for callers that cannot allocate device memory (code under CUDA graph capture, tight serving loops,
+ * harnesses that forbid cudaMalloc).  No counterpart in the reference.
+ * Same arguments and result as inksam_resize_u8 minus the workspace: the coefficient tables and the intermediate image
+ * live in a file-scope `static __device__` array of inksam_resize_static_max_bytes() = 16 MiB, which every GPU that
+ * loads the library holds until the process exits.  A resize whose inksam_resize_workspace_bytes(H, W, out_h, out_w)
+ * exceeds that (e.g. H * out_w * 3 > ~16 MB) is rejected with a non-zero return and inksam_last_error() set.  The call
+ * allocates and frees nothing.  All calls on a device share the array (it keeps the previous call's contents; nothing
+ * in it needs to start at zero): two calls that overlap on the GPU (different streams, no ordering) race. */
+size_t inksam_resize_static_max_bytes(void);
+int inksam_resize_u8_static(const uint8_t* src, int H, int W, long long src_row_pitch, uint8_t* dst, int out_h, int out_w,
+                            long long dst_row_pitch, void* stream);
+
 const char* inksam_last_error(void);
 
 #ifdef __cplusplus

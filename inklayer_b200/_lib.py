@@ -63,6 +63,8 @@ SIGNATURES = {
     "inksam_op_postprocess_packed": (c_int, [c_void_p, c_void_p, c_int, c_int, c_int, c_int, c_int, c_float, c_void_p]),
     "inksam_resize_workspace_bytes": (c_size_t, [c_int, c_int, c_int, c_int]),
     "inksam_resize_u8": (c_int, [c_void_p, c_int, c_int, c_longlong, c_void_p, c_int, c_int, c_longlong, c_void_p, c_void_p]),
+    "inksam_resize_static_max_bytes": (c_size_t, []),
+    "inksam_resize_u8_static": (c_int, [c_void_p, c_int, c_int, c_longlong, c_void_p, c_int, c_int, c_longlong, c_void_p]),
 }
 
 _lib = None

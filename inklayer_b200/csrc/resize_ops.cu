@@ -125,6 +125,33 @@ Plan make_plan(int H, int W, int out_h, int out_w) {
   return p;
 }
 
+// ------------------------------------------------------------------------------------------------ static scratch
+// Scratch of inksam_resize_u8_static: coefficient tables + the uint8 intermediate of the two-pass resample, in a file-scope
+// device array instead of a caller-owned workspace, for callers that cannot allocate (CUDA graph capture, serving loops).
+// Every GPU that loads the library holds these bytes until the process exits.  All calls share the array; nothing in it
+// has to start at zero (the coefficient kernels and the horizontal pass write every byte the later kernels read).
+constexpr size_t kStaticResizeBytes = (size_t)16 << 20;  // 16 MiB: e.g. a 4096 x 4096 x 3 source down to 1024 x 1024 (12.6 MB)
+static __device__ __align__(256) unsigned char g_resize_scratch[kStaticResizeBytes];
+
+// The array's name is a host-side stand-in in host code, not a device address: the address is looked up once per device,
+// with that device current, and cached.
+int static_resize_scratch(void** out) {
+  static void* ptr[kMaxDevices] = {};
+  static PerDeviceFlag have;
+  int dev = 0;
+  CUDA_TRY(cudaGetDevice(&dev));
+  if (dev < 0 || dev >= kMaxDevices) return set_error("inksam_resize_u8_static: device %d out of range", dev);
+  if (!have.done[dev]) {
+    void* p = nullptr;
+    CUDA_TRY(cudaGetSymbolAddress(&p, g_resize_scratch));
+    if (p == nullptr) return set_error("inksam_resize_u8_static: cudaGetSymbolAddress returned a null address");
+    ptr[dev] = p;
+    have.done[dev] = true;
+  }
+  *out = ptr[dev];
+  return 0;
+}
+
 }  // namespace
 }  // namespace inksam
 
@@ -175,6 +202,21 @@ int inksam_resize_u8(const uint8_t* src, int H, int W, long long src_row_pitch, 
   }
   CUDA_TRY(cudaGetLastError());
   return 0;
+}
+
+size_t inksam_resize_static_max_bytes(void) { return kStaticResizeBytes; }
+
+int inksam_resize_u8_static(const uint8_t* src, int H, int W, long long src_row_pitch, uint8_t* dst, int out_h, int out_w,
+                            long long dst_row_pitch, void* stream) {
+  if (H < 1 || W < 1 || out_h < 1 || out_w < 1)
+    return set_error("inksam_resize_u8_static: bad sizes %dx%d -> %dx%d", H, W, out_h, out_w);
+  const size_t need = make_plan(H, W, out_h, out_w).total;
+  if (need > kStaticResizeBytes)
+    return set_error("inksam_resize_u8_static: %dx%d -> %dx%d needs %zu bytes of scratch, the static array holds %zu "
+                     "(use inksam_resize_u8 with a caller-owned workspace)", H, W, out_h, out_w, need, kStaticResizeBytes);
+  void* scratch = nullptr;
+  INK_TRY(static_resize_scratch(&scratch));
+  return inksam_resize_u8(src, H, W, src_row_pitch, dst, out_h, out_w, dst_row_pitch, scratch, stream);
 }
 
 }  // extern "C"
