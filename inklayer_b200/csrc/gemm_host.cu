@@ -171,7 +171,7 @@ int launch_gemm(int cg, int tf32, int bn, int epi, const void* A, int lda, const
   CUtensorMap tO = tA;  // only the staged fp32 residual epilogue stores through a tensor map
   if (gemm_staged(epi)) {
     if ((reinterpret_cast<uintptr_t>(g.out) & 15) != 0 || (g.ldo * 4) % 16 != 0)
-      return set_error("gemm: the residual epilogue needs a 16-byte aligned output (ldo=%d)", g.ldo);
+      return set_error("gemm: epilogue %d stores its fp32 output by TMA and needs a 16-byte aligned output (ldo=%d)", epi, g.ldo);
     if (make_tmap_f32_out(&tO, g.out, g.M, g.N, g.ldo)) return -1;
   }
   CUtensorMap tX = tA;  // bf16 copy of the residual output

@@ -74,8 +74,9 @@ __host__ __device__ constexpr int gemm_epi_warps(int epi) {
   return (epi == EPI_LN_BF16_PAD || epi == EPI_LN_F32_NCHW) ? 4 : 8;
 }
 
-// ST != 0 (the fp32 residual epilogue): every epilogue warp owns two 2 KB staging buffers from which its 32-row x
-// 16-column fp32 sub-tiles leave by TMA store (32 KB in all; the CTA-pair ring keeps its 6 stages of 32 KB).
+// ST != 0 (the epilogues with fp32 row-major output): every epilogue warp owns two 2 KB staging buffers from which its
+// 32-row x 16-column fp32 sub-tiles leave by TMA store (32 KB in all; the CTA-pair ring keeps its 6 stages of 32 KB).
+// ST == 2 (EPI_RESID_LN_F32) also keeps the LayerNorm partials of the unstaged layout.
 template <int CG, int TF32, int BN, int ST = 0>
 struct GemmCfg {
   static constexpr int BM = 128;                 // rows per CTA (UMMA M = BM * CG)
@@ -84,7 +85,7 @@ struct GemmCfg {
   static constexpr int B_BYTES = BNL * 128;
   static constexpr int STAGE_BYTES = A_BYTES + B_BYTES;
   static constexpr int STAGING_BYTES = ST ? 8 * 2 * 2048 : 0;
-  static constexpr int AUX_BYTES = ST ? 256 /*barriers*/ : 256 /*barriers*/ + 4096 /*LN partials*/ + 1024 /*epilogue constants*/;
+  static constexpr int AUX_BYTES = ST == 1 ? 256 /*barriers*/ : 256 /*barriers*/ + 4096 /*LN partials*/ + 1024 /*epilogue constants*/;
   static constexpr int RING_BUDGET = ST ? (227 * 1024 - 1024 - AUX_BYTES - STAGING_BYTES) : 192 * 1024;
   static constexpr int STAGES = RING_BUDGET / STAGE_BYTES > 8 ? 8 : RING_BUDGET / STAGE_BYTES;
   static constexpr int KELEMS = TF32 ? 32 : 64;  // elements per 128-byte smem row
@@ -95,7 +96,12 @@ struct GemmCfg {
 
 __host__ __device__ constexpr bool epi_is_resid(int epi) { return epi == EPI_BIAS_RESID_F32 || epi == EPI_BIAS_RESID_STATS_F32; }
 __host__ __device__ constexpr bool epi_is_fold(int epi) { return epi == EPI_FOLD_BF16 || epi == EPI_FOLD_GELU_BF16; }
-__host__ __device__ constexpr int gemm_staged(int epi) { return epi_is_resid(epi) ? 1 : 0; }
+// fp32 row-major outputs leave through staging buffers and TMA stores: thread-per-row 32-byte stores put 32 sectors of 32
+// different lines into every instruction and held the decoder's image-side GEMMs at 70 % L1/LSU throughput and 38-49 % of
+// the HBM peak (ncu, round 2).
+__host__ __device__ constexpr int gemm_staged(int epi) {
+  return (epi_is_resid(epi) || epi == EPI_BIAS_ROWADD_F32 || epi == EPI_BIAS_F32) ? 1 : (epi == EPI_RESID_LN_F32 ? 2 : 0);
+}
 
 template <int CG, int TF32, int BN, int EPI>
 __global__ void __launch_bounds__(384, 1)
@@ -310,6 +316,30 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
       mbar_wait(tfull_bar(as), aphase);
       tc_fence_after();
 
+      // 32 rows x 32 fp32 columns of this warp (x = this thread's row) -> out[row0 .. row0+31][col .. col+31] through the warp's
+      // two 64B-swizzled staging halves and two TMA stores (rows >= M are clipped by the tensor map)
+      [[maybe_unused]] auto stage_chunk = [&](const float* x, int col) {
+        const uint32_t sbuf = staging_base + (uint32_t)(warp - 4) * 4096u;
+        const uint32_t srow = (uint32_t)lane * 64u, sx = (uint32_t)((lane >> 1) & 3);
+#pragma unroll
+        for (int hf = 0; hf < 2; ++hf) {
+          if (lane == 0) bulk_wait_group_read<1>();
+          __syncwarp();
+          const uint32_t sb = sbuf + (uint32_t)hf * 2048u;
+#pragma unroll
+          for (int j = 0; j < 4; ++j) {
+            const int e = hf * 16 + 4 * j;
+            st_shared_v4(sb + srow + (((uint32_t)j ^ sx) << 4), x[e], x[e + 1], x[e + 2], x[e + 3]);
+          }
+          fence_proxy_async_smem();
+          __syncwarp();
+          if (lane == 0) {
+            tma_store_2d(&tmO, sb, col + hf * 16, m - lane);
+            bulk_commit_group();
+          }
+        }
+      };
+
       if constexpr (epi_is_resid(EPI)) {
         // out = resid + acc + bias, fp32.  Thread-per-row global stores of a 32 x 32 fp32 sub-tile touch 32 lines per
         // instruction; instead each warp writes 32 x 16 halves into 64B-swizzled staging buffers (conflict-free 16-byte
@@ -447,20 +477,11 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
                 }
               }
             } else {
-              if (row_ok) {
-                float* o = reinterpret_cast<float*>(g.out) + (size_t)m * g.ldo + col;
+              if constexpr (kHasAdd) {
 #pragma unroll
-                for (int h = 0; h < 4; ++h) {
-                  uint32_t pk[8];
-#pragma unroll
-                  for (int j = 0; j < 8; ++j) {
-                    float x = f[h * 8 + j];
-                    if constexpr (kHasAdd) x += __uint_as_float(radd[ci & 1][h * 8 + j]);
-                    pk[j] = __float_as_uint(x);
-                  }
-                  st_global_v8(o + h * 8, pk);
-                }
+                for (int j = 0; j < 32; ++j) f[j] += __uint_as_float(radd[ci & 1][j]);
               }
+              stage_chunk(f, col);
             }
           }
         }
@@ -512,22 +533,16 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
           const int c = c_first + ci;
           tmem_ld_32x32(taddr + c * 32, v);
           tmem_ld_wait();
-          if (row_ok) {
-            float* o = reinterpret_cast<float*>(g.out) + (size_t)m * g.ldo + c * 32;
 #pragma unroll
-            for (int h = 0; h < 4; ++h) {
-              uint32_t pk[8];
-              const float4 w0 = __ldg(reinterpret_cast<const float4*>(g.ln_w + c * 32 + h * 8));
-              const float4 w1 = __ldg(reinterpret_cast<const float4*>(g.ln_w + c * 32 + h * 8 + 4));
-              const float4 b0 = __ldg(reinterpret_cast<const float4*>(g.ln_b + c * 32 + h * 8));
-              const float4 b1 = __ldg(reinterpret_cast<const float4*>(g.ln_b + c * 32 + h * 8 + 4));
-              const float ww[8] = {w0.x, w0.y, w0.z, w0.w, w1.x, w1.y, w1.z, w1.w};
-              const float bb[8] = {b0.x, b0.y, b0.z, b0.w, b1.x, b1.y, b1.z, b1.w};
-#pragma unroll
-              for (int j = 0; j < 8; ++j) pk[j] = __float_as_uint((f[h * 8 + j] - mean) * rstd * ww[j] + bb[j]);
-              st_global_v8(o + h * 8, pk);
-            }
+          for (int h = 0; h < 8; ++h) {
+            const float4 w0 = __ldg(reinterpret_cast<const float4*>(g.ln_w + c * 32 + h * 4));
+            const float4 b0 = __ldg(reinterpret_cast<const float4*>(g.ln_b + c * 32 + h * 4));
+            f[h * 4] = (f[h * 4] - mean) * rstd * w0.x + b0.x;
+            f[h * 4 + 1] = (f[h * 4 + 1] - mean) * rstd * w0.y + b0.y;
+            f[h * 4 + 2] = (f[h * 4 + 2] - mean) * rstd * w0.z + b0.z;
+            f[h * 4 + 3] = (f[h * 4 + 3] - mean) * rstd * w0.w + b0.w;
           }
+          stage_chunk(f, c * 32);
         }
       } else if constexpr (EPI == EPI_LN_BF16_PAD || EPI == EPI_LN_F32_NCHW) {
         // LayerNorm over the N == BN columns of this thread's row; the row lives in TMEM, so the three
@@ -684,7 +699,14 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
           tmem_ld_wait();
           float acc = 0.f;
 #pragma unroll
-          for (int j = 0; j < 32; ++j) acc += gelu_erf(f[j] + __ldg(g.bias + j)) * __ldg(hy + j);
+          for (int j = 0; j < 32; j += 4) {  // GELU on pairs (gelu_erf2: 7 instead of 12 FMA-pipe instructions per element)
+            const float4 b4 = __ldg(reinterpret_cast<const float4*>(g.bias + j));
+            const float4 h4 = __ldg(reinterpret_cast<const float4*>(hy + j));
+            float x0 = f[j] + b4.x, x1 = f[j + 1] + b4.y, x2 = f[j + 2] + b4.z, x3 = f[j + 3] + b4.w;
+            gelu_erf2(x0, x1);
+            gelu_erf2(x2, x3);
+            acc += x0 * h4.x; acc += x1 * h4.y; acc += x2 * h4.z; acc += x3 * h4.w;
+          }
           logit[spi] = acc;
         }
         if (row_ok) {
@@ -704,7 +726,7 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
   }
 
   // ---------------------------------------------------------------- teardown
-  if constexpr (epi_is_resid(EPI)) {
+  if constexpr (gemm_staged(EPI) != 0) {
     if (warp >= 4 && lane == 0) bulk_wait_group_all();  // this warp's TMA stores have left shared memory and are complete
   }
   tc_fence_before();
