@@ -55,21 +55,47 @@ __device__ __forceinline__ void linear_tok(float* __restrict__ out, int out_ld, 
         }
       }
     }
+    if constexpr (R * T > 16 && R * T <= 32) {
+      // Lane-sum of R * T (= 28) values per lane as a reduce-scatter: at offset 16 every lane hands half of its values to
+      // its partner and adds the other half's, then 8 values at offset 8, ... -- 31 shuffles and adds instead of 140, and lane
+      // i ends with the total of value i (= acc[i / T][i % T]) and writes it itself.  (With K = 256 the 140 shuffle-add pairs
+      // per 4 output rows outnumbered the 224 FMAs.)
+      float v[32];
 #pragma unroll
-    for (int r = 0; r < R; ++r)
+      for (int i = 0; i < 32; ++i) v[i] = i < R * T ? acc[i / T][i % T] : 0.f;
 #pragma unroll
-      for (int t = 0; t < T; ++t)
+      for (int off = 16; off >= 1; off >>= 1) {
+        const bool up = (lane & off) != 0;
 #pragma unroll
-        for (int o = 16; o > 0; o >>= 1) acc[r][t] += __shfl_xor_sync(0xffffffffu, acc[r][t], o);
-    if (lane == 0) {
+        for (int i = 0; i < off; ++i) {
+          const float send = up ? v[i] : v[i + off];
+          const float keep = up ? v[i + off] : v[i];
+          v[i] = keep + __shfl_xor_sync(0xffffffffu, send, off);
+        }
+      }
+      const int r = lane / T, t = lane % T;
+      if (lane < R * T && n0 + r < N) {
+        float o = v[0] + (bias ? bias[n0 + r] : 0.f);
+        if (relu) o = fmaxf(o, 0.f);
+        if (accumulate) out[t * out_ld + n0 + r] += o; else out[t * out_ld + n0 + r] = o;
+      }
+    } else {
 #pragma unroll
-      for (int r = 0; r < R; ++r) {
-        if (n0 + r < N) {
+      for (int r = 0; r < R; ++r)
 #pragma unroll
-          for (int t = 0; t < T; ++t) {
-            float v = acc[r][t] + (bias ? bias[n0 + r] : 0.f);
-            if (relu) v = fmaxf(v, 0.f);
-            if (accumulate) out[t * out_ld + n0 + r] += v; else out[t * out_ld + n0 + r] = v;
+        for (int t = 0; t < T; ++t)
+#pragma unroll
+          for (int o = 16; o > 0; o >>= 1) acc[r][t] += __shfl_xor_sync(0xffffffffu, acc[r][t], o);
+      if (lane == 0) {
+#pragma unroll
+        for (int r = 0; r < R; ++r) {
+          if (n0 + r < N) {
+#pragma unroll
+            for (int t = 0; t < T; ++t) {
+              float v = acc[r][t] + (bias ? bias[n0 + r] : 0.f);
+              if (relu) v = fmaxf(v, 0.f);
+              if (accumulate) out[t * out_ld + n0 + r] += v; else out[t * out_ld + n0 + r] = v;
+            }
           }
         }
       }
@@ -274,117 +300,108 @@ int launch_decoder_tokens(const DecWeights& w, const DecState& s, int boxes, int
 // box_img != null: the keys of box b are those of image box_img[b] (kv + box_img[b] * box_stride), shared by its boxes.
 //
 // HBM-bound (the per-box keys are read once: 4 MB per box and launch).  A CTA takes 512 consecutive keys of one box for
-// ALL heads: thread = (key row of a 32-row pass, head), so the 8 threads of a key read its 512 contiguous bytes of k
-// and of v and the CTA streams one contiguous 512-row range (a CTA per (box, head) read 64-byte slices at a 1-1.5 KB
-// stride and sat at a third of the HBM peak on DRAM page misses).  The 8 key ranges of a box are merged by the last
-// CTA to finish (ticket counter), in fixed order, so the result does not depend on scheduling.
+// ALL heads; thread = (key row of an 8-row pass, head, QUARTER of the head's 16 dims): a warp reads one key's 512
+// contiguous bytes of k and of v with one 16-byte load per lane, the thread's 4 dims of the 7 queries and of the 7
+// accumulators live in registers, and the four partial dot products of a head meet through two shuffles.  (The first
+// version had thread = (key, head): q re-read from shared memory for every key and 16-byte loads at a 64-byte stride kept
+// the L1 data pipe 75 % busy -- 243 k wavefronts per SM, half of them shared-memory reads -- at a third of the HBM peak, and
+// the launch over L2-resident shared keys took as long as the ones over per-box keys.)  The 8 key ranges of a box are
+// merged by the last CTA to finish (ticket counter), in fixed order, so the result does not depend on scheduling.
+__device__ __forceinline__ float fast_exp2(float x) {  // ex2.approx: one MUFU instruction, 2 ulp; exact 0 for x = -inf
+  float y;
+  asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(x));
+  return y;
+}
+
 constexpr int T2I_SPLITS = 8;                       // key ranges per box
 constexpr int T2I_PART = 8 * NT * 18;               // floats of one partial: [head][token][16 acc, l, m]
-constexpr int T2I_QP = 20;                          // padded head row of q in shared memory (conflict-free LDS.128)
 
 __global__ void __launch_bounds__(256) decoder_t2i_kernel(const float* __restrict__ q, const float* __restrict__ kv,
                                                           long long box_stride, int ld, const int* __restrict__ box_img,
                                                           float* __restrict__ out, float* __restrict__ partial,
                                                           int* __restrict__ ticket) {
   const int box = blockIdx.y, split = blockIdx.x, tid = threadIdx.x;
-  const int h = tid & 7, kr = tid >> 3, warp = tid >> 5, lane = tid & 31;
-  __shared__ __align__(16) float qs[NT * 8 * T2I_QP];
+  const int warp = tid >> 5, lane = tid & 31, h = lane >> 2, qt = lane & 3;  // lane = float4 index inside a 128-float row
   __shared__ float red_m[8][8 * NT];
   __shared__ float red[8][8 * NT * 17];
   __shared__ int last;
-  for (int i = tid; i < NT * 128; i += 256) {  // 1/sqrt(16) and log2(e) folded into q
-    const int t = i >> 7, c = i & 127;
-    qs[(t * 8 + (c >> 4)) * T2I_QP + (c & 15)] = q[(size_t)box * NT * 128 + i] * (0.25f * 1.4426950408889634f);
+  float4 q4[NT], acc[NT];
+  float m[NT], l[NT];
+#pragma unroll
+  for (int t = 0; t < NT; ++t) {  // 1/sqrt(16) and log2(e) folded into q
+    q4[t] = __ldg(reinterpret_cast<const float4*>(q + (size_t)box * NT * 128 + t * 128) + lane);
+    q4[t].x *= 0.25f * 1.4426950408889634f; q4[t].y *= 0.25f * 1.4426950408889634f;
+    q4[t].z *= 0.25f * 1.4426950408889634f; q4[t].w *= 0.25f * 1.4426950408889634f;
+    acc[t] = make_float4(0.f, 0.f, 0.f, 0.f);
+    m[t] = 0.f; l[t] = 0.f;
   }
-  __syncthreads();
-  const float* base = kv + (size_t)(box_img ? box_img[box] : box) * box_stride + (size_t)split * 512 * ld + h * 16;
-  const uint32_t qs_addr = (uint32_t)__cvta_generic_to_shared(&qs[0]) + (uint32_t)(h * T2I_QP * 4);
-  float m[NT], l[NT], acc[NT][16];
+  const float* base = kv + (size_t)(box_img ? box_img[box] : box) * box_stride + (size_t)split * 512 * ld;
+  // 64 passes of 8 keys (one per warp) with the next two passes in flight.  The softmax shift of a token is lazy: it is set
+  // by the first key and moves (with a rescale of l and acc) only when a later score exceeds it by more than 2^24 -- tested
+  // once per key for all 7 tokens -- so the common path is one ex2.approx and 9 FMAs per (token, key) and thread.
+  float4 nk[2], nv[2];
 #pragma unroll
-  for (int t = 0; t < NT; ++t) {
-    m[t] = -INFINITY; l[t] = 0.f;
-#pragma unroll
-    for (int d = 0; d < 16; ++d) acc[t][d] = 0.f;
+  for (int i = 0; i < 2; ++i) {
+    const float4* r = reinterpret_cast<const float4*>(base + (size_t)(warp + 8 * i) * ld);
+    nk[i] = r[lane]; nv[i] = r[32 + lane];
   }
-  // 16 passes of 32 keys with the next pass already in flight.  The softmax shift of a token is lazy: it is set by the
-  // first key and moves (with an exact rescale of l and acc) only when a later score exceeds it by more than 2^24, so
-  // the common path is one exp2 and 17 FMAs per (token, key).
-  float4 nk[4], nv[4];
-  {
-    const float4* r = reinterpret_cast<const float4*>(base + (size_t)kr * ld);
 #pragma unroll
-    for (int i = 0; i < 4; ++i) { nk[i] = r[i]; nv[i] = r[32 + i]; }
+  for (int t = 0; t < NT; ++t) {  // the shift of a token starts at its score with this warp's first key
+    float x = q4[t].x * nk[0].x + q4[t].y * nk[0].y + q4[t].z * nk[0].z + q4[t].w * nk[0].w;
+    x += __shfl_xor_sync(0xffffffffu, x, 1);
+    x += __shfl_xor_sync(0xffffffffu, x, 2);
+    m[t] = x;
   }
-#pragma unroll 1
-  for (int j = kr; j < 512; j += 32) {
-    float kk[16], vv[16];
-#pragma unroll
-    for (int i = 0; i < 4; ++i) {
-      kk[4 * i] = nk[i].x; kk[4 * i + 1] = nk[i].y; kk[4 * i + 2] = nk[i].z; kk[4 * i + 3] = nk[i].w;
-      vv[4 * i] = nv[i].x; vv[4 * i + 1] = nv[i].y; vv[4 * i + 2] = nv[i].z; vv[4 * i + 3] = nv[i].w;
+#pragma unroll 2
+  for (int i = 0; i < 64; ++i) {
+    const float4 kk = nk[i & 1], vv = nv[i & 1];
+    if (i + 2 < 64) {
+      const float4* r = reinterpret_cast<const float4*>(base + (size_t)(warp + 8 * (i + 2)) * ld);
+      nk[i & 1] = r[lane]; nv[i & 1] = r[32 + lane];
     }
-    if (j + 32 < 512) {
-      const float4* r = reinterpret_cast<const float4*>(base + (size_t)(j + 32) * ld);
+    float sc[NT], over = -INFINITY;
 #pragma unroll
-      for (int i = 0; i < 4; ++i) { nk[i] = r[i]; nv[i] = r[32 + i]; }
+    for (int t = 0; t < NT; ++t) {
+      float x = q4[t].x * kk.x + q4[t].y * kk.y + q4[t].z * kk.z + q4[t].w * kk.w;
+      x += __shfl_xor_sync(0xffffffffu, x, 1);
+      x += __shfl_xor_sync(0xffffffffu, x, 2);  // the four lanes of a head hold the same score
+      sc[t] = x - m[t];
+      over = fmaxf(over, sc[t]);
+    }
+    if (over > 24.f) {  // one test per key (cold): a score far above some token's shift -> move that shift there
+#pragma unroll
+      for (int t = 0; t < NT; ++t) {
+        if (sc[t] > 24.f) {
+          const float corr = fast_exp2(-sc[t]);
+          m[t] += sc[t];
+          l[t] *= corr;
+          acc[t].x *= corr; acc[t].y *= corr; acc[t].z *= corr; acc[t].w *= corr;
+          sc[t] = 0.f;
+        }
+      }
     }
 #pragma unroll
     for (int t = 0; t < NT; ++t) {
-      float sc = 0.f;
-#pragma unroll
-      for (int i = 0; i < 4; ++i) {
-        // q stays in shared memory (LDS.128, re-read per key): in registers it would be 112 more live values on top
-        // of the 112 accumulators
-        float4 q4;
-        asm volatile("ld.shared.v4.f32 {%0, %1, %2, %3}, [%4];"
-                     : "=f"(q4.x), "=f"(q4.y), "=f"(q4.z), "=f"(q4.w)
-                     : "r"(qs_addr + (uint32_t)((t * 8 * T2I_QP + 4 * i) * 4)));
-        sc += q4.x * kk[4 * i] + q4.y * kk[4 * i + 1] + q4.z * kk[4 * i + 2] + q4.w * kk[4 * i + 3];
-      }
-      if (sc > m[t] + 24.f) {  // first key (m = -inf) or a much larger score: move the shift
-        const float corr = exp2f(m[t] - sc);  // 0 for the first key
-        m[t] = sc;
-        l[t] *= corr;
-#pragma unroll
-        for (int d = 0; d < 16; ++d) acc[t][d] *= corr;
-      }
-      const float p = exp2f(sc - m[t]);
+      const float p = fast_exp2(sc[t]);
       l[t] += p;
-#pragma unroll
-      for (int d = 0; d < 16; ++d) acc[t][d] += p * vv[d];
+      acc[t].x += p * vv.x; acc[t].y += p * vv.y; acc[t].z += p * vv.z; acc[t].w += p * vv.w;
     }
   }
-  // merge the 32 partial softmaxes of every head: the lanes of a warp with equal (lane & 7) share a head
-  float gm[NT];
+  // merge the 8 warps (each holds the softmax state of its 64 keys for every head and token)
+  if (qt == 0) {
 #pragma unroll
-  for (int t = 0; t < NT; ++t) {
-    float v = m[t];
-    v = fmaxf(v, __shfl_xor_sync(0xffffffffu, v, 8));
-    v = fmaxf(v, __shfl_xor_sync(0xffffffffu, v, 16));
-    if (lane < 8) red_m[warp][h * NT + t] = v;
+    for (int t = 0; t < NT; ++t) red_m[warp][h * NT + t] = m[t];
   }
   __syncthreads();
 #pragma unroll
   for (int t = 0; t < NT; ++t) {
-    float v = red_m[0][h * NT + t];
+    float gm = red_m[0][h * NT + t];
 #pragma unroll
-    for (int w2 = 1; w2 < 8; ++w2) v = fmaxf(v, red_m[w2][h * NT + t]);
-    gm[t] = v;
-  }
-#pragma unroll
-  for (int t = 0; t < NT; ++t) {
-    const float sc = exp2f(m[t] - gm[t]);
-    float v = l[t] * sc;
-    v += __shfl_xor_sync(0xffffffffu, v, 8);
-    v += __shfl_xor_sync(0xffffffffu, v, 16);
-    if (lane < 8) red[warp][(h * NT + t) * 17 + 16] = v;
-#pragma unroll
-    for (int d = 0; d < 16; ++d) {
-      float a = acc[t][d] * sc;
-      a += __shfl_xor_sync(0xffffffffu, a, 8);
-      a += __shfl_xor_sync(0xffffffffu, a, 16);
-      if (lane < 8) red[warp][(h * NT + t) * 17 + d] = a;
-    }
+    for (int w2 = 1; w2 < 8; ++w2) gm = fmaxf(gm, red_m[w2][h * NT + t]);
+    const float sc = exp2f(m[t] - gm);
+    float* r = &red[warp][(h * NT + t) * 17];
+    r[qt * 4] = acc[t].x * sc; r[qt * 4 + 1] = acc[t].y * sc; r[qt * 4 + 2] = acc[t].z * sc; r[qt * 4 + 3] = acc[t].w * sc;
+    if (qt == 0) r[16] = l[t] * sc;
   }
   __syncthreads();
   // this key range's partial: [head][token][16 acc, l, m]
@@ -444,71 +461,69 @@ size_t decoder_t2i_scratch_floats(int boxes) { return (size_t)boxes * T2I_SPLITS
 // ------------------------------------------------------------------------------------------------ image -> token
 // Every image token attends to the 7 tokens (8 heads x 16). q: column `qcol` of the kvq rows (stride ld, box_stride 0
 // when shared); kv: [box][2][7][128]. out: [box*4096][128] fp32, the A operand of the out_proj GEMM.
+//
+// HBM-bound by design (512 B read + 512 B written per pixel), but the first version -- thread = (pixel, head), k / v of the
+// 7 tokens re-read from shared memory for every pixel (56 LDS.128 per thread and pixel) and 16-byte global accesses at a
+// 64-byte stride -- kept the L1 data pipe 80 % busy (281 k wavefronts per SM, ncu) and reached a third of the HBM peak.
+// Now thread = (pixel, head, QUARTER of the head's 16 dims): the thread's 4 dims of k and v of the 7 tokens live in registers
+// for the whole block (no shared memory in the loop), a warp reads / writes one pixel's 512 contiguous bytes with one
+// 16-byte access per lane, and the four partial dot products of a head meet through two shuffles.
+constexpr int I2T_PIX = 512;  // pixels per block
+
 __global__ void __launch_bounds__(256) decoder_i2t_kernel(const float* __restrict__ qsrc, long long box_stride, int ld, int qcol,
                                                           const int* __restrict__ box_img, const float* __restrict__ kv,
                                                           float* __restrict__ out) {
-  const int box = blockIdx.y, tid = threadIdx.x;
-  // k / v of the 7 tokens, head rows padded 16 -> 20 floats: the 8 lanes of a quarter warp (8 heads of one pixel) then
-  // read 8 disjoint 4-bank groups with one LDS.128 each (conflict-free; an unpadded row is a 4-way conflict)
-  constexpr int HP = 20;
-  __shared__ __align__(16) float ks[NT * 8 * HP], vs[NT * 8 * HP];
-  for (int i = tid; i < NT * 128; i += 256) {
-    const int t = i >> 7, c = i & 127;
-    ks[(t * 8 + (c >> 4)) * HP + (c & 15)] = kv[(size_t)box * 2 * NT * 128 + i];
-    vs[(t * 8 + (c >> 4)) * HP + (c & 15)] = kv[(size_t)box * 2 * NT * 128 + NT * 128 + i];
-  }
-  __syncthreads();
-  const int h = tid & 7;
-#pragma unroll 1
-  for (int rep = 0; rep < 4; ++rep) {  // 4 x 32 pixels per block
-    const int pix = blockIdx.x * 128 + rep * 32 + (tid >> 3);
-    const float4* qr = reinterpret_cast<const float4*>(qsrc + (size_t)(box_img ? box_img[box] : box) * box_stride +
-                                                       (size_t)pix * ld + qcol + h * 16);
-    float qv[16];
+  const int box = blockIdx.y, tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+  // lane = head * 4 + quarter = float4 index inside the 128-float row
+  float4 k4[NT], v4[NT];
+  {
+    const float4* kp = reinterpret_cast<const float4*>(kv + (size_t)box * 2 * NT * 128);
 #pragma unroll
-    for (int i = 0; i < 4; ++i) {
-      const float4 a = qr[i];
-      qv[4 * i] = a.x; qv[4 * i + 1] = a.y; qv[4 * i + 2] = a.z; qv[4 * i + 3] = a.w;
+    for (int t = 0; t < NT; ++t) {
+      k4[t] = __ldg(kp + t * 32 + lane);
+      v4[t] = __ldg(kp + NT * 32 + t * 32 + lane);
+      k4[t].x *= 0.25f * 1.4426950408889634f; k4[t].y *= 0.25f * 1.4426950408889634f;  // 1/sqrt(16) and log2(e) folded into k
+      k4[t].z *= 0.25f * 1.4426950408889634f; k4[t].w *= 0.25f * 1.4426950408889634f;
     }
+  }
+  const float* qbase = qsrc + (size_t)(box_img ? box_img[box] : box) * box_stride + qcol;
+  const int pix0 = blockIdx.x * I2T_PIX + warp;
+  float4* obase = reinterpret_cast<float4*>(out + (size_t)box * 4096 * 128);
+  constexpr int NP = I2T_PIX / 8;  // pixels per warp
+  float4 qn[2];
+  qn[0] = *(reinterpret_cast<const float4*>(qbase + (size_t)pix0 * ld) + lane);
+  qn[1] = *(reinterpret_cast<const float4*>(qbase + (size_t)(pix0 + 8) * ld) + lane);
+#pragma unroll 2
+  for (int i = 0; i < NP; ++i) {
+    const int pix = pix0 + i * 8;
+    const float4 q = qn[i & 1];
+    if (i + 2 < NP) qn[i & 1] = *(reinterpret_cast<const float4*>(qbase + (size_t)(pix + 16) * ld) + lane);
     float sc[NT], mx = -INFINITY;
 #pragma unroll
     for (int t = 0; t < NT; ++t) {
-      const float4* kr = reinterpret_cast<const float4*>(ks + (t * 8 + h) * HP);
-      float s = 0.f;
-#pragma unroll
-      for (int i = 0; i < 4; ++i) {
-        const float4 k4 = kr[i];
-        s += qv[4 * i] * k4.x + qv[4 * i + 1] * k4.y + qv[4 * i + 2] * k4.z + qv[4 * i + 3] * k4.w;
-      }
-      sc[t] = s * 0.25f;
-      mx = fmaxf(mx, sc[t]);
+      float x = q.x * k4[t].x + q.y * k4[t].y + q.z * k4[t].z + q.w * k4[t].w;
+      x += __shfl_xor_sync(0xffffffffu, x, 1);
+      x += __shfl_xor_sync(0xffffffffu, x, 2);  // all four lanes of the head hold the same sum
+      sc[t] = x;
+      mx = fmaxf(mx, x);
     }
     float sum = 0.f;
 #pragma unroll
-    for (int t = 0; t < NT; ++t) { sc[t] = expf(sc[t] - mx); sum += sc[t]; }
-    const float inv = 1.f / sum;
-    float o[16];
-#pragma unroll
-    for (int d = 0; d < 16; ++d) o[d] = 0.f;
+    for (int t = 0; t < NT; ++t) { sc[t] = fast_exp2(sc[t] - mx); sum += sc[t]; }
+    const float inv = __fdividef(1.f, sum);
+    float4 o = make_float4(0.f, 0.f, 0.f, 0.f);
 #pragma unroll
     for (int t = 0; t < NT; ++t) {
       const float p = sc[t] * inv;
-      const float4* vr = reinterpret_cast<const float4*>(vs + (t * 8 + h) * HP);
-#pragma unroll
-      for (int i = 0; i < 4; ++i) {
-        const float4 v4 = vr[i];
-        o[4 * i] += p * v4.x; o[4 * i + 1] += p * v4.y; o[4 * i + 2] += p * v4.z; o[4 * i + 3] += p * v4.w;
-      }
+      o.x += p * v4[t].x; o.y += p * v4[t].y; o.z += p * v4[t].z; o.w += p * v4[t].w;
     }
-    float4* dst = reinterpret_cast<float4*>(out + ((size_t)box * 4096 + pix) * 128 + h * 16);
-#pragma unroll
-    for (int i = 0; i < 4; ++i) dst[i] = make_float4(o[4 * i], o[4 * i + 1], o[4 * i + 2], o[4 * i + 3]);
+    obase[(size_t)pix * 32 + lane] = o;
   }
 }
 
 int launch_decoder_i2t(const float* qsrc, long long box_stride, int ld, int qcol, const int* box_img, const float* kv,
                        float* out, int boxes, cudaStream_t st) {
-  decoder_i2t_kernel<<<dim3(32, boxes), 256, 0, st>>>(qsrc, box_stride, ld, qcol, box_img, kv, out);
+  decoder_i2t_kernel<<<dim3(4096 / I2T_PIX, boxes), 256, 0, st>>>(qsrc, box_stride, ld, qcol, box_img, kv, out);
   CUDA_TRY(cudaGetLastError());
   return 0;
 }
