@@ -344,6 +344,7 @@ int finalize_decoder(inksam_handle* h, cudaStream_t st) {
     c.tf32 = 1; c.bn = 128; c.epi = EPI_BIAS_F32;
     c.A = h->pe; c.lda = 256; c.W = wra; c.ldw = 256;
     c.g.M = 4096; c.g.N = N; c.g.K = 256; c.g.ldo = N; c.g.out = ra;
+    c.g.bias = bm;  // the projection bias rides in the row-add table: one operand less in the k|v|q GEMM's epilogue
     INK_TRY(run_gemm(h, c, st));
     if (fin) { h->wkvf = wm; h->bkvf = bm; h->raf = ra; }
     else { h->wkvq[l] = wm; h->bkvq[l] = bm; h->ra[l] = ra; }
@@ -636,7 +637,7 @@ int decode_chunk(inksam_handle* h, const float* keys0, const float* kvq0, char* 
   // ---- layer 1: per-box keys
   {
     G c; c.tf32 = 1; c.bn = 128; c.epi = EPI_BIAS_ROWADD_F32; c.A = keysb; c.lda = 256; c.W = h->wkvq[1]; c.ldw = 256;
-    c.g.M = Mb; c.g.N = 384; c.g.K = 256; c.g.ldo = 384; c.g.out = kvq; c.g.bias = h->bkvq[1]; c.g.rowadd = h->ra[1];
+    c.g.M = Mb; c.g.N = 384; c.g.K = 256; c.g.ldo = 384; c.g.out = kvq; c.g.bias = nullptr; c.g.rowadd = h->ra[1];
     c.g.rowadd_mod = 4096;
     INK_TRY(run_gemm(h, c, st));
   }
@@ -648,7 +649,7 @@ int decode_chunk(inksam_handle* h, const float* keys0, const float* kvq0, char* 
   // ---- final token -> image attention
   {
     G c; c.tf32 = 1; c.epi = EPI_BIAS_ROWADD_F32; c.A = keysb; c.lda = 256; c.W = h->wkvf; c.ldw = 256;
-    c.g.M = Mb; c.g.N = 256; c.g.K = 256; c.g.ldo = 256; c.g.out = kvq; c.g.bias = h->bkvf; c.g.rowadd = h->raf;
+    c.g.M = Mb; c.g.N = 256; c.g.K = 256; c.g.ldo = 256; c.g.out = kvq; c.g.bias = nullptr; c.g.rowadd = h->raf;
     c.g.rowadd_mod = 4096;
     INK_TRY(run_gemm(h, c, st));
   }
@@ -754,7 +755,7 @@ int decode_batch_impl(inksam_handle* h, const float* embeddings, int B, const fl
   INK_TRY(launch_decoder_keys0(embeddings, nomask, keys0, B, st));
   {
     G c; c.tf32 = 1; c.bn = 128; c.epi = EPI_BIAS_ROWADD_F32; c.A = keys0; c.lda = 256; c.W = h->wkvq[0]; c.ldw = 256;
-    c.g.M = B * 4096; c.g.N = 384; c.g.K = 256; c.g.ldo = 384; c.g.out = kvq0; c.g.bias = h->bkvq[0]; c.g.rowadd = h->ra[0];
+    c.g.M = B * 4096; c.g.N = 384; c.g.K = 256; c.g.ldo = 384; c.g.out = kvq0; c.g.bias = nullptr; c.g.rowadd = h->ra[0];
     c.g.rowadd_mod = 4096;
     INK_TRY(run_gemm(h, c, st));
   }

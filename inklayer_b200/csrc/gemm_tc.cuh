@@ -85,7 +85,7 @@ struct GemmCfg {
   static constexpr int B_BYTES = BNL * 128;
   static constexpr int STAGE_BYTES = A_BYTES + B_BYTES;
   static constexpr int STAGING_BYTES = ST ? 8 * 2 * 2048 : 0;
-  static constexpr int AUX_BYTES = ST == 1 ? 256 /*barriers*/ : 256 /*barriers*/ + 4096 /*LN partials*/ + 1024 /*epilogue constants*/;
+  static constexpr int AUX_BYTES = ST == 1 ? 256 /*barriers*/ : 256 /*barriers*/ + 4096 /*LN partials*/ + 3072 /*epilogue constants*/;
   static constexpr int RING_BUDGET = ST ? (227 * 1024 - 1024 - AUX_BYTES - STAGING_BYTES) : 192 * 1024;
   static constexpr int STAGES = RING_BUDGET / STAGE_BYTES > 8 ? 8 : RING_BUDGET / STAGE_BYTES;
   static constexpr int KELEMS = TF32 ? 32 : 64;  // elements per 128-byte smem row
@@ -159,6 +159,15 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
     if (threadIdx.x >= 128 && threadIdx.x < 192) {
       const int c = threadIdx.x - 128;
       ec[c] = g.bias[c]; ec[64 + c] = g.ln_w[c]; ec[128 + c] = g.ln_b[c];
+    }
+  }
+  // EPI_RESID_LN_F32: bias, LayerNorm weight and bias of the 256 columns.  As __ldg loads in the epilogue they sat on its
+  // critical path behind the streaming residual loads (L1 misses: a fifth of the epilogue warps' stall samples, ncu).
+  if constexpr (EPI == EPI_RESID_LN_F32) {
+    float* ec = reinterpret_cast<float*>(smem_raw + (econst - smem_u32(smem_raw)));
+    if (threadIdx.x >= 128) {
+      const int c = threadIdx.x - 128;  // 0..255
+      ec[c] = g.bias[c]; ec[256 + c] = g.ln_w[c]; ec[512 + c] = g.ln_b[c];
     }
   }
   tc_fence_before();
@@ -316,6 +325,11 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
       mbar_wait(tfull_bar(as), aphase);
       tc_fence_after();
 
+      [[maybe_unused]] auto lds4c = [](uint32_t addr) {  // broadcast read of epilogue constants (volatile: not hoisted into registers)
+        float4 r;
+        asm volatile("ld.shared.v4.f32 {%0, %1, %2, %3}, [%4];" : "=f"(r.x), "=f"(r.y), "=f"(r.z), "=f"(r.w) : "r"(addr));
+        return r;
+      };
       // 32 rows x 32 fp32 columns of this warp (x = this thread's row) -> out[row0 .. row0+31][col .. col+31] through the warp's
       // two 64B-swizzled staging halves and two TMA stores (rows >= M are clipped by the tensor map)
       [[maybe_unused]] auto stage_chunk = [&](const float* x, int col) {
@@ -510,7 +524,7 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
           tmem_ld_wait();
 #pragma unroll
           for (int j = 0; j < 32; j += 4) {
-            const float4 b4 = __ldg(reinterpret_cast<const float4*>(g.bias + c * 32 + j));
+            const float4 b4 = lds4c(econst + 4 * (c * 32 + j));
             f[j] += b4.x + __uint_as_float(rr[ci & 1][j]);
             f[j + 1] += b4.y + __uint_as_float(rr[ci & 1][j + 1]);
             f[j + 2] += b4.z + __uint_as_float(rr[ci & 1][j + 2]);
@@ -535,8 +549,8 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
           tmem_ld_wait();
 #pragma unroll
           for (int h = 0; h < 8; ++h) {
-            const float4 w0 = __ldg(reinterpret_cast<const float4*>(g.ln_w + c * 32 + h * 4));
-            const float4 b0 = __ldg(reinterpret_cast<const float4*>(g.ln_b + c * 32 + h * 4));
+            const float4 w0 = lds4c(econst + 4 * (256 + c * 32 + h * 4));
+            const float4 b0 = lds4c(econst + 4 * (512 + c * 32 + h * 4));
             f[h * 4] = (f[h * 4] - mean) * rstd * w0.x + b0.x;
             f[h * 4 + 1] = (f[h * 4 + 1] - mean) * rstd * w0.y + b0.y;
             f[h * 4 + 2] = (f[h * 4 + 2] - mean) * rstd * w0.z + b0.z;
