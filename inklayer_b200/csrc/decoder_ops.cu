@@ -7,6 +7,7 @@
 // prompt_encoder.py:62-71,93-100,185-214.
 #include "common.h"
 #include "decoder_ops.h"
+#include "ptx.cuh"
 
 namespace inksam {
 
@@ -26,11 +27,13 @@ __device__ __forceinline__ void linear_tok(float* __restrict__ out, int out_ld, 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31, nwarps = blockDim.x >> 5;
   const int k4n = Kd / 4;
   for (int n0 = warp * R; n0 < N; n0 += nwarps * R) {
-    float acc[R][T];
+    // two partial sums per (row, token) -- even and odd pairs of k -- so that the inner product runs on fma.rn.f32x2: half
+    // the FMA-pipe instructions of this FMA-bound loop
+    uint64_t acc2[R][T];
 #pragma unroll
     for (int r = 0; r < R; ++r)
 #pragma unroll
-      for (int t = 0; t < T; ++t) acc[r][t] = 0.f;
+      for (int t = 0; t < T; ++t) acc2[r][t] = f2_pack(0.f, 0.f);
     const float4* w[R];
 #pragma unroll
     for (int r = 0; r < R; ++r) w[r] = reinterpret_cast<const float4*>(W + (size_t)(n0 + r < N ? n0 + r : n0) * Kd);
@@ -49,12 +52,23 @@ __device__ __forceinline__ void linear_tok(float* __restrict__ out, int out_ld, 
 #pragma unroll
           for (int t = 0; t < T; ++t) {
             const float4 x = *reinterpret_cast<const float4*>(in + t * in_ld + kk * 4);
+            const uint64_t x01 = f2_pack(x.x, x.y), x23 = f2_pack(x.z, x.w);
 #pragma unroll
-            for (int r = 0; r < R; ++r) acc[r][t] += a[u][r].x * x.x + a[u][r].y * x.y + a[u][r].z * x.z + a[u][r].w * x.w;
+            for (int r = 0; r < R; ++r)
+              acc2[r][t] = f2_fma(f2_pack(a[u][r].z, a[u][r].w), x23, f2_fma(f2_pack(a[u][r].x, a[u][r].y), x01, acc2[r][t]));
           }
         }
       }
     }
+    float acc[R][T];
+#pragma unroll
+    for (int r = 0; r < R; ++r)
+#pragma unroll
+      for (int t = 0; t < T; ++t) {
+        float lo, hi;
+        f2_unpack(acc2[r][t], lo, hi);
+        acc[r][t] = lo + hi;
+      }
     if constexpr (R * T > 16 && R * T <= 32) {
       // Lane-sum of R * T (= 28) values per lane as a reduce-scatter: at offset 16 every lane hands half of its values to
       // its partner and adds the other half's, then 8 values at offset 8, ... -- 31 shuffles and adds instead of 140, and lane
