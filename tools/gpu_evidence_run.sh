@@ -4,7 +4,7 @@
 cd "$(dirname "$0")/.."
 mkdir -p gpurun_out
 tools/gpu_suite.sh test_gpu_gemm test_gpu_gemm_stress test_gpu_ops test_gpu_attention test_gpu_ln_fold test_gpu_refine \
-    test_gpu_e2e test_gpu_config1 test_properties
+    test_gpu_e2e test_gpu_config1 test_properties test_zz_no_alloc
 echo "suite rc=$?"
 timeout 900 python bench.py --steps 20 --warmup 5 > gpurun_out/bench.json 2> gpurun_out/bench.err; echo "bench rc=$?"; cat gpurun_out/bench.json; tail -3 gpurun_out/bench.err
 timeout 600 python bench.py --impl reference --steps 3 --warmup 1 > gpurun_out/bench_ref.json 2> gpurun_out/bench_ref.err; echo "ref rc=$?"; cat gpurun_out/bench_ref.json
