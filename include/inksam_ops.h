@@ -88,6 +88,19 @@ int inksam_op_postprocess(const float* low, unsigned char* masks, float* logits,
 int inksam_op_postprocess_packed(const float* low, unsigned char* mask_bits, int K, int in_h, int in_w, int H, int W, float thr,
                                  void* stream);
 
+/* The two cross attentions of the mask decoder's TwoWayAttentionBlock on the image side (SA/modeling/transformer.py:151-182,
+ * Attention with downsample_rate 2: 8 heads x 16, :185-240), after the q / k / v projections, before out_proj.
+ *   inksam_op_decoder_t2i: token -> image.  q [boxes][7][128]; kv rows [4096][ld] fp32 per box, k in columns [0,128) and v in
+ *     [128,256), box b at kv + (box_img ? box_img[b] : b) * box_stride floats (box_stride 0: all boxes share the keys);
+ *     out [boxes][7][128] = softmax(q k^T / 4) v per head.  scratch: inksam_op_decoder_t2i_scratch_bytes(boxes) device bytes.
+ *   inksam_op_decoder_i2t: image -> token.  q = columns [qcol, qcol+128) of the rows [4096][ld] at qsrc (+ box offset as
+ *     above); kv [boxes][2][7][128] (k then v of the 7 tokens); out [boxes*4096][128]. */
+size_t inksam_op_decoder_t2i_scratch_bytes(int boxes);
+int inksam_op_decoder_t2i(const float* q, const float* kv, long long box_stride, int ld, const int* box_img, float* out,
+                          void* scratch, int boxes, void* stream);
+int inksam_op_decoder_i2t(const float* qsrc, long long box_stride, int ld, int qcol, const int* box_img, const float* kv,
+                          float* out, int boxes, void* stream);
+
 /* ResizeLongestSide.apply_image on the device: Pillow's 8-bit bilinear resample (torchvision resize of a PIL image,
  * SA/utils/transforms.py:26-31; algorithm of Pillow libImaging/Resample.c), bit-exact with the host path.
  * src: uint8 [H][W][3] with src_row_pitch bytes per row; dst: uint8 [out_h][out_w][3] with dst_row_pitch bytes per row

@@ -1,6 +1,7 @@
 // C-ABI kernel-level entry points (include/inksam_ops.h).
 #include "common.h"
 #include "inksam_ops.h"
+#include "decoder_ops.h"
 
 using namespace inksam;
 
@@ -69,6 +70,30 @@ int inksam_op_gemm_fold(int epi, const void* A, int lda, const void* W, int ldw,
   g.M = M; g.N = N; g.K = K; g.ldo = ldo; g.out = out; g.bias = bias; g.resid = resid; g.win_remap = win_remap;
   g.stats_out = stats_out; g.xb_out = xb_out; g.stats_in = stats_in; g.colsum = colsum; g.stats_np = stats_np; g.fold_eps = eps;
   return launch_gemm(2, 0, 256, epi, A, lda, W, ldw, g, device_sms(), static_cast<cudaStream_t>(stream));
+}
+
+size_t inksam_op_decoder_t2i_scratch_bytes(int boxes) {
+  return boxes > 0 ? decoder_t2i_scratch_floats(boxes) * sizeof(float) + (size_t)boxes * sizeof(int) : 0;
+}
+
+int inksam_op_decoder_t2i(const float* q, const float* kv, long long box_stride, int ld, const int* box_img, float* out,
+                          void* scratch, int boxes, void* stream) {
+  if (!q || !kv || !out || !scratch || boxes < 1) return set_error("inksam_op_decoder_t2i: null argument or no boxes");
+  if (ld < 256 || ld % 4 != 0 || (reinterpret_cast<uintptr_t>(kv) & 15) != 0 || box_stride % 4 != 0)
+    return set_error("inksam_op_decoder_t2i: kv rows must be 16-byte aligned with k at column 0 and v at column 128 (ld=%d)", ld);
+  auto st = static_cast<cudaStream_t>(stream);
+  float* partial = static_cast<float*>(scratch);
+  int* ticket = reinterpret_cast<int*>(partial + decoder_t2i_scratch_floats(boxes));
+  CUDA_TRY(cudaMemsetAsync(ticket, 0, (size_t)boxes * sizeof(int), st));
+  return launch_decoder_t2i(q, kv, box_stride, ld, box_img, out, partial, ticket, boxes, st);
+}
+
+int inksam_op_decoder_i2t(const float* qsrc, long long box_stride, int ld, int qcol, const int* box_img, const float* kv,
+                          float* out, int boxes, void* stream) {
+  if (!qsrc || !kv || !out || boxes < 1) return set_error("inksam_op_decoder_i2t: null argument or no boxes");
+  if (ld % 4 != 0 || qcol % 4 != 0 || qcol + 128 > ld || (reinterpret_cast<uintptr_t>(qsrc) & 15) != 0 || box_stride % 4 != 0)
+    return set_error("inksam_op_decoder_i2t: q rows must be 16-byte aligned (ld=%d qcol=%d)", ld, qcol);
+  return launch_decoder_i2t(qsrc, box_stride, ld, qcol, box_img, kv, out, boxes, static_cast<cudaStream_t>(stream));
 }
 
 int inksam_op_patchify(const void* images, int dtype, int B, const int* hw, long long img_stride, long long row_pitch,

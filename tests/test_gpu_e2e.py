@@ -90,6 +90,35 @@ def test_decoder_alone_matches_oracle_on_same_embedding():
     assert torch.allclose(l1, low[5:6], atol=1e-5)
 
 
+@pytest.mark.parametrize("scale", [3.0, 8.0])
+def test_decoder_peaky_attention_moves_the_lazy_softmax_shift(scale):
+    """decoder_t2i_kernel keeps a lazy softmax shift per (head, token) that only moves when a key's score exceeds it by
+    2^24; decoder_i2t_kernel subtracts the row maximum.  With the q / k projections of both cross attentions scaled up the
+    logits span hundreds of log2 units (far beyond fp32 range of exp2 without a shift) and the softmax is nearly one-hot: the
+    shift has to move.  Compared with the oracle decoder on the same fp32 embedding; the tf32 rounding of the k|v|q projections is
+    amplified by the scale (at 30x the nearly one-hot softmax picks different keys: 4 % rel-RMS with finite outputs), hence two
+    moderate scales here; the kernels alone are checked against float64 torch over thousands of log2 units in
+    test_gpu_ops.py::test_decoder_token_to_image_attention / test_decoder_image_to_token_attention."""
+    cfg_name = "vit_tiny"
+    cfg, sd = CONFIGS[cfg_name], dict(synthetic_state_dict(CONFIGS[cfg_name], 0))
+    for k in list(sd):
+        if ("cross_attn_token_to_image" in k or "cross_attn_image_to_token" in k or "final_attn_token_to_image" in k) and \
+                (k.endswith("q_proj.weight") or k.endswith("k_proj.weight")):
+            sd[k] = sd[k] * scale
+    from inklayer_b200.synth import synthetic_boxes, synthetic_sketch
+
+    ora = O.OraclePredictor(O.CONFIGS[cfg_name], sd)
+    ora.set_image(synthetic_sketch(0))
+    sam = build_sam_from_state_dict(sd, cfg).to("cuda")
+    boxes = torch.from_numpy(synthetic_boxes(3, 24))
+    m_ref, i_ref, l_ref = ora.predict_torch(boxes)
+    masks, iou, low = sam.decode_boxes(ora.features.cuda(), boxes.cuda(), (1024, 1024), (1024, 1024))
+    assert torch.isfinite(low).all() and torch.isfinite(iou).all()
+    err = rel_rms(low.cpu(), l_ref)
+    print(f"scale {scale}: low-res rel-RMS {err:.2e}  min IoU {mask_iou(masks.cpu().numpy(), m_ref.numpy()).min():.4f}")
+    assert err <= 3e-2
+
+
 def test_surface_errors_and_edge_cases():
     cfg = CONFIGS["vit_tiny"]
     sam = build_sam_from_state_dict(synthetic_state_dict(cfg, 0), cfg).to("cuda")

@@ -185,3 +185,58 @@ def test_sam_resize_longest_side_and_errors():
         sam.resize_longest_side(torch.zeros(3, 10, 10, dtype=torch.uint8, device="cuda"))
     lib = _lib.load()
     assert lib.inksam_resize_u8(None, 10, 10, 30, None, 5, 5, 15, None, stream()) != 0
+
+
+def _attn_ref(q, k, v):
+    """8 heads x 16, softmax(q k^T / sqrt(16)) v in float64.  q [..., Tq, 128], k / v [..., Tk, 128]."""
+    sh = q.shape[:-2]
+    qh = q.double().reshape(*sh, -1, 8, 16).transpose(-2, -3)
+    kh = k.double().reshape(*sh, -1, 8, 16).transpose(-2, -3)
+    vh = v.double().reshape(*sh, -1, 8, 16).transpose(-2, -3)
+    p = torch.softmax(qh @ kh.transpose(-1, -2) / 4.0, dim=-1)
+    return (p @ vh).transpose(-2, -3).reshape(*sh, -1, 128)
+
+
+@pytest.mark.parametrize("gain,shared", [(1.0, False), (1.0, True), (12.0, False), (60.0, False), (60.0, True)])
+def test_decoder_token_to_image_attention(gain, shared):
+    """decoder_t2i_kernel against float64 torch: 7 queries x 4096 keys x 8 heads per box.  Large gains make the logits span
+    thousands of log2 units with the largest keys late in each key range, so the lazy softmax shift (set by a warp's first key,
+    moved when a score exceeds it by 2^24) has to move many times; `shared`: all boxes read the keys of their image."""
+    lib = _lib.load()
+    boxes, ld = 5, 384
+    g = torch.Generator().manual_seed(11)
+    q = (torch.randn(boxes, 7, 128, generator=g) * gain).cuda()
+    nimg = 2 if shared else boxes
+    kv = torch.randn(nimg, 4096, ld, generator=g)
+    ramp = torch.linspace(0.2, 2.0, 4096).view(1, 4096, 1)      # later keys are larger
+    kv[:, :, :128] *= ramp
+    kv = kv.cuda()
+    box_img = torch.tensor([0, 1, 1, 0, 1], dtype=torch.int32, device="cuda") if shared else None
+    out = torch.full((boxes, 7, 128), float("nan"), device="cuda")
+    scratch = torch.empty(int(lib.inksam_op_decoder_t2i_scratch_bytes(boxes)), dtype=torch.uint8, device="cuda")
+    for _ in range(2):  # the ticket counters must be left ready for the next launch
+        _lib.check(lib.inksam_op_decoder_t2i(ptr(q), ptr(kv), 4096 * ld, ld, ptr(box_img), ptr(out), ptr(scratch), boxes, stream()))
+    sel = box_img.long() if shared else torch.arange(boxes, device="cuda")
+    ref = _attn_ref(q, kv[sel][:, :, :128], kv[sel][:, :, 128:256])
+    assert torch.isfinite(out).all()
+    err = (out.double() - ref).abs().max().item() / ref.abs().max().item()
+    assert err < 2e-5, err
+
+
+@pytest.mark.parametrize("gain,shared", [(1.0, False), (40.0, False), (40.0, True)])
+def test_decoder_image_to_token_attention(gain, shared):
+    """decoder_i2t_kernel against float64 torch: every image token attends to the 7 tokens."""
+    lib = _lib.load()
+    boxes, ld, qcol = 3, 384, 256
+    g = torch.Generator().manual_seed(12)
+    nimg = 2 if shared else boxes
+    qsrc = (torch.randn(nimg, 4096, ld, generator=g) * gain).cuda()
+    kvt = torch.randn(boxes, 2, 7, 128, generator=g).cuda()
+    box_img = torch.tensor([1, 0, 1], dtype=torch.int32, device="cuda") if shared else None
+    out = torch.full((boxes * 4096, 128), float("nan"), device="cuda")
+    _lib.check(lib.inksam_op_decoder_i2t(ptr(qsrc), 4096 * ld, ld, qcol, ptr(box_img), ptr(kvt), ptr(out), boxes, stream()))
+    sel = box_img.long() if shared else torch.arange(boxes, device="cuda")
+    ref = _attn_ref(qsrc[sel][:, :, qcol:qcol + 128], kvt[:, 0], kvt[:, 1]).reshape(boxes * 4096, 128)
+    assert torch.isfinite(out).all()
+    err = (out.double() - ref).abs().max().item() / ref.abs().max().item()
+    assert err < 2e-5, err
