@@ -302,7 +302,7 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
             if constexpr (epi_is_resid(EPI))
               ld_global_v8_stream(add_row + c_first * 32 + h * 8, *reinterpret_cast<uint32_t(*)[8]>(&radd[0][h * 8]));
             else
-              ld_global_v8(add_row + c_first * 32 + h * 8, *reinterpret_cast<uint32_t(*)[8]>(&radd[0][h * 8]));
+              ld_global_v8_stream(add_row + c_first * 32 + h * 8, *reinterpret_cast<uint32_t(*)[8]>(&radd[0][h * 8]));
           }
         }
       }
@@ -454,7 +454,7 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
               if (ci + 1 < NCW && col + 32 < g.N) {
 #pragma unroll
                 for (int h = 0; h < 4; ++h)
-                  ld_global_v8(add_row + (c + 1) * 32 + h * 8, *reinterpret_cast<uint32_t(*)[8]>(&radd[(ci + 1) & 1][h * 8]));
+                  ld_global_v8_stream(add_row + (c + 1) * 32 + h * 8, *reinterpret_cast<uint32_t(*)[8]>(&radd[(ci + 1) & 1][h * 8]));
               }
             }
             tmem_ld_wait();
@@ -510,7 +510,7 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
         if (g.row_img != nullptr && row_ok) mm += __ldg(g.row_img + m / g.resid_mod) * g.resid_mod;
         const float* rrow = g.resid + (size_t)mm * g.ldo;
 #pragma unroll
-        for (int h = 0; h < 4; ++h) ld_global_v8(rrow + c_first * 32 + h * 8, *reinterpret_cast<uint32_t(*)[8]>(&rr[0][h * 8]));
+        for (int h = 0; h < 4; ++h) ld_global_v8_stream(rrow + c_first * 32 + h * 8, *reinterpret_cast<uint32_t(*)[8]>(&rr[0][h * 8]));
         float sum = 0.f, sq = 0.f;
 #pragma unroll
         for (int ci = 0; ci < NCW; ++ci) {
@@ -519,7 +519,7 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
           if (ci + 1 < NCW) {
 #pragma unroll
             for (int h = 0; h < 4; ++h)
-              ld_global_v8(rrow + (c + 1) * 32 + h * 8, *reinterpret_cast<uint32_t(*)[8]>(&rr[(ci + 1) & 1][h * 8]));
+              ld_global_v8_stream(rrow + (c + 1) * 32 + h * 8, *reinterpret_cast<uint32_t(*)[8]>(&rr[(ci + 1) & 1][h * 8]));
           }
           tmem_ld_wait();
 #pragma unroll
