@@ -91,15 +91,22 @@ int inksam_op_postprocess_packed(const float* low, unsigned char* mask_bits, int
 /* The two cross attentions of the mask decoder's TwoWayAttentionBlock on the image side (SA/modeling/transformer.py:151-182,
  * Attention with downsample_rate 2: 8 heads x 16, :185-240), after the q / k / v projections, before out_proj.
  *   inksam_op_decoder_t2i: token -> image.  q [boxes][7][128]; kv rows [4096][ld] fp32 per box, k in columns [0,128) and v in
- *     [128,256), box b at kv + (box_img ? box_img[b] : b) * box_stride floats (box_stride 0: all boxes share the keys);
+ *     [128,256), box b at kv + (box_img ? box_img[b] : b) * box_stride elements (box_stride 0: all boxes share the keys);
  *     out [boxes][7][128] = softmax(q k^T / 4) v per head.  scratch: inksam_op_decoder_t2i_scratch_bytes(boxes) device bytes.
  *   inksam_op_decoder_i2t: image -> token.  q = columns [qcol, qcol+128) of the rows [4096][ld] at qsrc (+ box offset as
  *     above); kv [boxes][2][7][128] (k then v of the 7 tokens); out [boxes*4096][128]. */
 size_t inksam_op_decoder_t2i_scratch_bytes(int boxes);
-int inksam_op_decoder_t2i(const float* q, const float* kv, long long box_stride, int ld, const int* box_img, float* out,
+int inksam_op_decoder_t2i(const float* q, const void* kv, int kv_half, long long box_stride, int ld, const int* box_img, float* out,
                           void* scratch, int boxes, void* stream);
-int inksam_op_decoder_i2t(const float* qsrc, long long box_stride, int ld, int qcol, const int* box_img, const float* kv,
+int inksam_op_decoder_i2t(const void* qsrc, int q_half, long long box_stride, int ld, int qcol, const int* box_img, const float* kv,
                           float* out, int boxes, void* stream);
+/* kv_half / q_half != 0: the k|v|q rows are fp16 (as inksam_op_gemm_rowadd_f16 writes them) instead of fp32; box_stride, ld and
+ * qcol count elements either way.  The engine stores the per-box k|v|q of the decoder that way: they are written once by a tf32
+ * GEMM and read once by these kernels' fp32 FMAs, and fp16 keeps the 10 explicit mantissa bits of a tf32 operand.
+ * inksam_op_gemm_rowadd_f16: the tcgen05 GEMM with the row-add epilogue (inksam_op_gemm, epi 3) storing
+ * out_f16[m][n] = fp16(acc + bias[n] + rowadd[m % rowadd_mod][n]), round to nearest, saturating at +-65504. */
+int inksam_op_gemm_rowadd_f16(int cg, int tf32, int bn, const void* A, int lda, const void* W, int ldw, int M, int N, int K,
+                              void* out_f16, int ldo, const float* bias, const float* rowadd, int rowadd_mod, void* stream);
 
 /* ResizeLongestSide.apply_image on the device: Pillow's 8-bit bilinear resample (torchvision resize of a PIL image,
  * SA/utils/transforms.py:26-31; algorithm of Pillow libImaging/Resample.c), bit-exact with the host path.

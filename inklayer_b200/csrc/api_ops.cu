@@ -28,6 +28,13 @@ int inksam_op_gemm(int cg, int tf32, int bn, int epi, const void* A, int lda, co
   return launch_gemm(cg, tf32, bn, epi, A, lda, W, ldw, g, device_sms(), static_cast<cudaStream_t>(stream));
 }
 
+int inksam_op_gemm_rowadd_f16(int cg, int tf32, int bn, const void* A, int lda, const void* W, int ldw, int M, int N, int K,
+                              void* out_f16, int ldo, const float* bias, const float* rowadd, int rowadd_mod, void* stream) {
+  GemmArgs g{};
+  g.M = M; g.N = N; g.K = K; g.ldo = ldo; g.out = out_f16; g.bias = bias; g.rowadd = rowadd; g.rowadd_mod = rowadd_mod; g.out_f16 = 1;
+  return launch_gemm(cg, tf32, bn, EPI_BIAS_ROWADD_F32, A, lda, W, ldw, g, device_sms(), static_cast<cudaStream_t>(stream));
+}
+
 int inksam_op_attention(int windowed, const void* qkv, const void* rel, void* out, int B, int heads, int head_dim, void* stream) {
   return launch_attention(windowed, qkv, rel, out, B, heads, head_dim, static_cast<cudaStream_t>(stream));
 }
@@ -76,7 +83,7 @@ size_t inksam_op_decoder_t2i_scratch_bytes(int boxes) {
   return boxes > 0 ? decoder_t2i_scratch_floats(boxes) * sizeof(float) + (size_t)boxes * sizeof(int) : 0;
 }
 
-int inksam_op_decoder_t2i(const float* q, const float* kv, long long box_stride, int ld, const int* box_img, float* out,
+int inksam_op_decoder_t2i(const float* q, const void* kv, int kv_half, long long box_stride, int ld, const int* box_img, float* out,
                           void* scratch, int boxes, void* stream) {
   if (!q || !kv || !out || !scratch || boxes < 1) return set_error("inksam_op_decoder_t2i: null argument or no boxes");
   if (ld < 256 || ld % 4 != 0 || (reinterpret_cast<uintptr_t>(kv) & 15) != 0 || box_stride % 4 != 0)
@@ -85,15 +92,15 @@ int inksam_op_decoder_t2i(const float* q, const float* kv, long long box_stride,
   float* partial = static_cast<float*>(scratch);
   int* ticket = reinterpret_cast<int*>(partial + decoder_t2i_scratch_floats(boxes));
   CUDA_TRY(cudaMemsetAsync(ticket, 0, (size_t)boxes * sizeof(int), st));
-  return launch_decoder_t2i(q, kv, box_stride, ld, box_img, out, partial, ticket, boxes, st);
+  return launch_decoder_t2i(q, kv, kv_half, box_stride, ld, box_img, out, partial, ticket, boxes, st);
 }
 
-int inksam_op_decoder_i2t(const float* qsrc, long long box_stride, int ld, int qcol, const int* box_img, const float* kv,
+int inksam_op_decoder_i2t(const void* qsrc, int q_half, long long box_stride, int ld, int qcol, const int* box_img, const float* kv,
                           float* out, int boxes, void* stream) {
   if (!qsrc || !kv || !out || boxes < 1) return set_error("inksam_op_decoder_i2t: null argument or no boxes");
   if (ld % 4 != 0 || qcol % 4 != 0 || qcol + 128 > ld || (reinterpret_cast<uintptr_t>(qsrc) & 15) != 0 || box_stride % 4 != 0)
     return set_error("inksam_op_decoder_i2t: q rows must be 16-byte aligned (ld=%d qcol=%d)", ld, qcol);
-  return launch_decoder_i2t(qsrc, box_stride, ld, qcol, box_img, kv, out, boxes, static_cast<cudaStream_t>(stream));
+  return launch_decoder_i2t(qsrc, q_half, box_stride, ld, qcol, box_img, kv, out, boxes, static_cast<cudaStream_t>(stream));
 }
 
 int inksam_op_patchify(const void* images, int dtype, int B, const int* hw, long long img_stride, long long row_pitch,

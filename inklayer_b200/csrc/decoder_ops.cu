@@ -5,6 +5,7 @@
 //
 // Reference: SA/modeling/transformer.py:62-106,151-182,218-240; mask_decoder.py:112-149,154-176;
 // prompt_encoder.py:62-71,93-100,185-214.
+#include <cuda_fp16.h>
 #include "common.h"
 #include "decoder_ops.h"
 #include "ptx.cuh"
@@ -330,10 +331,28 @@ __device__ __forceinline__ float fast_exp2(float x) {  // ex2.approx: one MUFU i
 constexpr int T2I_SPLITS = 8;                       // key ranges per box
 constexpr int T2I_PART = 8 * NT * 18;               // floats of one partial: [head][token][16 acc, l, m]
 
-__global__ void __launch_bounds__(256) decoder_t2i_kernel(const float* __restrict__ q, const float* __restrict__ kv,
+// 4 consecutive elements of a k|v|q row for this lane: fp32 (16 bytes) or fp16 (8 bytes; GemmArgs::out_f16).  The prefetch
+// queues of the kernels below hold the raw loaded words (and are twice as deep for fp16, so that the bytes in flight per SM
+// stay the same: with half the bytes per load the fp16 variants were latency-bound at 1.3 TB/s).
+template <bool HALF> struct Row4 { using Raw = float4; static constexpr int DEPTH = 2; };
+template <> struct Row4<true> { using Raw = uint2; static constexpr int DEPTH = 4; };
+template <bool HALF>
+__device__ __forceinline__ typename Row4<HALF>::Raw load_row4(const void* row, int idx4) {
+  return *(reinterpret_cast<const typename Row4<HALF>::Raw*>(row) + idx4);
+}
+__device__ __forceinline__ float4 cvt_row4(const float4& r) { return r; }
+__device__ __forceinline__ float4 cvt_row4(const uint2& u) {
+  const float2 a = __half22float2(*reinterpret_cast<const __half2*>(&u.x));
+  const float2 b = __half22float2(*reinterpret_cast<const __half2*>(&u.y));
+  return make_float4(a.x, a.y, b.x, b.y);
+}
+
+template <bool HALF>
+__global__ void __launch_bounds__(256) decoder_t2i_kernel(const float* __restrict__ q, const void* __restrict__ kv_,
                                                           long long box_stride, int ld, const int* __restrict__ box_img,
                                                           float* __restrict__ out, float* __restrict__ partial,
                                                           int* __restrict__ ticket) {
+  constexpr int ES = HALF ? 2 : 4;  // bytes per element of the kv rows (box_stride and ld are in elements)
   const int box = blockIdx.y, split = blockIdx.x, tid = threadIdx.x;
   const int warp = tid >> 5, lane = tid & 31, h = lane >> 2, qt = lane & 3;  // lane = float4 index inside a 128-float row
   __shared__ float red_m[8][8 * NT];
@@ -349,29 +368,31 @@ __global__ void __launch_bounds__(256) decoder_t2i_kernel(const float* __restric
     acc[t] = make_float4(0.f, 0.f, 0.f, 0.f);
     m[t] = 0.f; l[t] = 0.f;
   }
-  const float* base = kv + (size_t)(box_img ? box_img[box] : box) * box_stride + (size_t)split * 512 * ld;
+  const char* base = static_cast<const char*>(kv_) + ((size_t)(box_img ? box_img[box] : box) * box_stride + (size_t)split * 512 * ld) * ES;
   // 64 passes of 8 keys (one per warp) with the next two passes in flight.  The softmax shift of a token is lazy: it is set
   // by the first key and moves (with a rescale of l and acc) only when a later score exceeds it by more than 2^24 -- tested
   // once per key for all 7 tokens -- so the common path is one ex2.approx and 9 FMAs per (token, key) and thread.
-  float4 nk[2], nv[2];
+  constexpr int PD = Row4<HALF>::DEPTH;
+  typename Row4<HALF>::Raw nk[PD], nv[PD];
 #pragma unroll
-  for (int i = 0; i < 2; ++i) {
-    const float4* r = reinterpret_cast<const float4*>(base + (size_t)(warp + 8 * i) * ld);
-    nk[i] = r[lane]; nv[i] = r[32 + lane];
+  for (int i = 0; i < PD; ++i) {
+    const char* r = base + (size_t)(warp + 8 * i) * ld * ES;
+    nk[i] = load_row4<HALF>(r, lane); nv[i] = load_row4<HALF>(r, 32 + lane);
   }
 #pragma unroll
   for (int t = 0; t < NT; ++t) {  // the shift of a token starts at its score with this warp's first key
-    float x = q4[t].x * nk[0].x + q4[t].y * nk[0].y + q4[t].z * nk[0].z + q4[t].w * nk[0].w;
+    const float4 k0 = cvt_row4(nk[0]);
+    float x = q4[t].x * k0.x + q4[t].y * k0.y + q4[t].z * k0.z + q4[t].w * k0.w;
     x += __shfl_xor_sync(0xffffffffu, x, 1);
     x += __shfl_xor_sync(0xffffffffu, x, 2);
     m[t] = x;
   }
-#pragma unroll 2
+#pragma unroll PD
   for (int i = 0; i < 64; ++i) {
-    const float4 kk = nk[i & 1], vv = nv[i & 1];
-    if (i + 2 < 64) {
-      const float4* r = reinterpret_cast<const float4*>(base + (size_t)(warp + 8 * (i + 2)) * ld);
-      nk[i & 1] = r[lane]; nv[i & 1] = r[32 + lane];
+    const float4 kk = cvt_row4(nk[i % PD]), vv = cvt_row4(nv[i % PD]);
+    if (i + PD < 64) {
+      const char* r = base + (size_t)(warp + 8 * (i + PD)) * ld * ES;
+      nk[i % PD] = load_row4<HALF>(r, lane); nv[i % PD] = load_row4<HALF>(r, 32 + lane);
     }
     float sc[NT], over = -INFINITY;
 #pragma unroll
@@ -463,9 +484,10 @@ __global__ void __launch_bounds__(256) decoder_t2i_kernel(const float* __restric
 
 // partial: boxes * T2I_SPLITS * T2I_PART floats of scratch; ticket: boxes ints, zero before the first launch (the
 // kernel leaves them zero).
-int launch_decoder_t2i(const float* q, const float* kv, long long box_stride, int ld, const int* box_img, float* out,
+int launch_decoder_t2i(const float* q, const void* kv, int kv_half, long long box_stride, int ld, const int* box_img, float* out,
                        float* partial, int* ticket, int boxes, cudaStream_t st) {
-  decoder_t2i_kernel<<<dim3(T2I_SPLITS, boxes), 256, 0, st>>>(q, kv, box_stride, ld, box_img, out, partial, ticket);
+  if (kv_half) decoder_t2i_kernel<true><<<dim3(T2I_SPLITS, boxes), 256, 0, st>>>(q, kv, box_stride, ld, box_img, out, partial, ticket);
+  else decoder_t2i_kernel<false><<<dim3(T2I_SPLITS, boxes), 256, 0, st>>>(q, kv, box_stride, ld, box_img, out, partial, ticket);
   CUDA_TRY(cudaGetLastError());
   return 0;
 }
@@ -484,9 +506,11 @@ size_t decoder_t2i_scratch_floats(int boxes) { return (size_t)boxes * T2I_SPLITS
 // 16-byte access per lane, and the four partial dot products of a head meet through two shuffles.
 constexpr int I2T_PIX = 512;  // pixels per block
 
-__global__ void __launch_bounds__(256) decoder_i2t_kernel(const float* __restrict__ qsrc, long long box_stride, int ld, int qcol,
+template <bool HALF>
+__global__ void __launch_bounds__(256) decoder_i2t_kernel(const void* __restrict__ qsrc, long long box_stride, int ld, int qcol,
                                                           const int* __restrict__ box_img, const float* __restrict__ kv,
                                                           float* __restrict__ out) {
+  constexpr int ES = HALF ? 2 : 4;
   const int box = blockIdx.y, tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
   // lane = head * 4 + quarter = float4 index inside the 128-float row
   float4 k4[NT], v4[NT];
@@ -500,18 +524,19 @@ __global__ void __launch_bounds__(256) decoder_i2t_kernel(const float* __restric
       k4[t].z *= 0.25f * 1.4426950408889634f; k4[t].w *= 0.25f * 1.4426950408889634f;
     }
   }
-  const float* qbase = qsrc + (size_t)(box_img ? box_img[box] : box) * box_stride + qcol;
+  const char* qbase = static_cast<const char*>(qsrc) + ((size_t)(box_img ? box_img[box] : box) * box_stride + qcol) * ES;
   const int pix0 = blockIdx.x * I2T_PIX + warp;
   float4* obase = reinterpret_cast<float4*>(out + (size_t)box * 4096 * 128);
   constexpr int NP = I2T_PIX / 8;  // pixels per warp
-  float4 qn[2];
-  qn[0] = *(reinterpret_cast<const float4*>(qbase + (size_t)pix0 * ld) + lane);
-  qn[1] = *(reinterpret_cast<const float4*>(qbase + (size_t)(pix0 + 8) * ld) + lane);
-#pragma unroll 2
+  constexpr int PD = Row4<HALF>::DEPTH;
+  typename Row4<HALF>::Raw qn[PD];
+#pragma unroll
+  for (int i = 0; i < PD; ++i) qn[i] = load_row4<HALF>(qbase + (size_t)(pix0 + 8 * i) * ld * ES, lane);
+#pragma unroll PD
   for (int i = 0; i < NP; ++i) {
     const int pix = pix0 + i * 8;
-    const float4 q = qn[i & 1];
-    if (i + 2 < NP) qn[i & 1] = *(reinterpret_cast<const float4*>(qbase + (size_t)(pix + 16) * ld) + lane);
+    const float4 q = cvt_row4(qn[i % PD]);
+    if (i + PD < NP) qn[i % PD] = load_row4<HALF>(qbase + (size_t)(pix + 8 * PD) * ld * ES, lane);
     float sc[NT], mx = -INFINITY;
 #pragma unroll
     for (int t = 0; t < NT; ++t) {
@@ -535,9 +560,10 @@ __global__ void __launch_bounds__(256) decoder_i2t_kernel(const float* __restric
   }
 }
 
-int launch_decoder_i2t(const float* qsrc, long long box_stride, int ld, int qcol, const int* box_img, const float* kv,
+int launch_decoder_i2t(const void* qsrc, int q_half, long long box_stride, int ld, int qcol, const int* box_img, const float* kv,
                        float* out, int boxes, cudaStream_t st) {
-  decoder_i2t_kernel<<<dim3(4096 / I2T_PIX, boxes), 256, 0, st>>>(qsrc, box_stride, ld, qcol, box_img, kv, out);
+  if (q_half) decoder_i2t_kernel<true><<<dim3(4096 / I2T_PIX, boxes), 256, 0, st>>>(qsrc, box_stride, ld, qcol, box_img, kv, out);
+  else decoder_i2t_kernel<false><<<dim3(4096 / I2T_PIX, boxes), 256, 0, st>>>(qsrc, box_stride, ld, qcol, box_img, kv, out);
   CUDA_TRY(cudaGetLastError());
   return 0;
 }

@@ -45,10 +45,11 @@ struct BoxSegments {
 };
 
 int launch_decoder_tokens(const DecWeights& w, const DecState& s, int boxes, int phase, int layer, cudaStream_t st);
-int launch_decoder_t2i(const float* q, const float* kv, long long box_stride, int ld, const int* box_img, float* out,
+// kv_half / q_half: the k|v|q rows are fp16 (GemmArgs::out_f16) instead of fp32; box_stride and ld count elements either way
+int launch_decoder_t2i(const float* q, const void* kv, int kv_half, long long box_stride, int ld, const int* box_img, float* out,
                        float* partial, int* ticket, int boxes, cudaStream_t st);
 size_t decoder_t2i_scratch_floats(int boxes);  // floats of `partial`; `ticket` is `boxes` ints, zeroed once
-int launch_decoder_i2t(const float* qsrc, long long box_stride, int ld, int qcol, const int* box_img, const float* kv,
+int launch_decoder_i2t(const void* qsrc, int q_half, long long box_stride, int ld, int qcol, const int* box_img, const float* kv,
                        float* out, int boxes, cudaStream_t st);
 int launch_decoder_keys0(const float* emb, const float* nomask, float* keys, int B, cudaStream_t st);
 int launch_box_image_index(const BoxSegments& seg, int* box_img, cudaStream_t st);

@@ -607,13 +607,14 @@ int decode_chunk(inksam_handle* h, const float* keys0, const float* kvq0, char* 
   const int Mb = n * 4096;
 
   auto tokens = [&](int phase, int layer) { ++h->launches; return launch_decoder_tokens(h->dec, s, n, phase, layer, st); };
-  auto t2i = [&](const float* kv, long long stride, int ld, const int* bi) {
+  // per-box k|v|q (layer 1 and the final attention) are stored as fp16: written once by a tf32 GEMM, read once by fp32 FMAs
+  auto t2i = [&](const void* kv, int half, long long stride, int ld, const int* bi) {
     ++h->launches;
-    return launch_decoder_t2i(s.q_t2i, kv, stride, ld, bi, s.attn_t2i, t2i_part, t2i_ticket, n, st);
+    return launch_decoder_t2i(s.q_t2i, kv, half, stride, ld, bi, s.attn_t2i, t2i_part, t2i_ticket, n, st);
   };
-  auto i2t = [&](const float* q, long long stride, const int* bi) {
+  auto i2t = [&](const void* q, int half, long long stride, const int* bi) {
     ++h->launches;
-    return launch_decoder_i2t(q, stride, 384, 256, bi, s.kv_i2t, a1, n, st);
+    return launch_decoder_i2t(q, half, stride, 384, 256, bi, s.kv_i2t, a1, n, st);
   };
   // keys <- norm4(keys + out_proj(image->token attention))   (transformer.py:176-180)
   auto keys_update = [&](int layer, const float* resid, int resid_mod, const int* row_img) -> int {
@@ -630,31 +631,31 @@ int decode_chunk(inksam_handle* h, const float* keys0, const float* kvq0, char* 
 
   // ---- layer 0: the image-side k / v / q are shared by all boxes of an image (kvq0)
   INK_TRY(tokens(0, 0));
-  INK_TRY(t2i(kvq0, 4096LL * 384, 384, bimg));
+  INK_TRY(t2i(kvq0, 0, 4096LL * 384, 384, bimg));
   INK_TRY(tokens(2, 0));
-  INK_TRY(i2t(kvq0, 4096LL * 384, bimg));
+  INK_TRY(i2t(kvq0, 0, 4096LL * 384, bimg));
   INK_TRY(keys_update(0, keys0, 4096, bimg));
   // ---- layer 1: per-box keys
   {
     G c; c.tf32 = 1; c.bn = 128; c.epi = EPI_BIAS_ROWADD_F32; c.A = keysb; c.lda = 256; c.W = h->wkvq[1]; c.ldw = 256;
     c.g.M = Mb; c.g.N = 384; c.g.K = 256; c.g.ldo = 384; c.g.out = kvq; c.g.bias = nullptr; c.g.rowadd = h->ra[1];
-    c.g.rowadd_mod = 4096;
+    c.g.rowadd_mod = 4096; c.g.out_f16 = 1;
     INK_TRY(run_gemm(h, c, st));
   }
   INK_TRY(tokens(1, 1));
-  INK_TRY(t2i(kvq, 4096LL * 384, 384, nullptr));
+  INK_TRY(t2i(kvq, 1, 4096LL * 384, 384, nullptr));
   INK_TRY(tokens(2, 1));
-  INK_TRY(i2t(kvq, 4096LL * 384, nullptr));
+  INK_TRY(i2t(kvq, 1, 4096LL * 384, nullptr));
   INK_TRY(keys_update(1, keysb, 0, nullptr));
   // ---- final token -> image attention
   {
     G c; c.tf32 = 1; c.epi = EPI_BIAS_ROWADD_F32; c.A = keysb; c.lda = 256; c.W = h->wkvf; c.ldw = 256;
     c.g.M = Mb; c.g.N = 256; c.g.K = 256; c.g.ldo = 256; c.g.out = kvq; c.g.bias = nullptr; c.g.rowadd = h->raf;
-    c.g.rowadd_mod = 4096;
+    c.g.rowadd_mod = 4096; c.g.out_f16 = 1;
     INK_TRY(run_gemm(h, c, st));
   }
   INK_TRY(tokens(3, 0));
-  INK_TRY(t2i(kvq, 4096LL * 256, 256, nullptr));
+  INK_TRY(t2i(kvq, 1, 4096LL * 256, 256, nullptr));
   INK_TRY(tokens(4, 0));
   // ---- upscaling: ConvT(256->64,k2,s2)+LayerNorm2d+GELU, ConvT(64->32,k2,s2)+GELU, dot with the hypernetwork vector
   const float *u0w, *u0b, *u1w, *u1b, *u3w, *u3b;

@@ -49,6 +49,9 @@ struct GemmArgs {
   const float* colsum;    // [N] sum over k of the bf16 weight row (with stats_in; `bias` then holds b + W beta)
   int stats_np;           // partials per row in stats_in
   float fold_eps;         // eps of the folded LayerNorm
+  int out_f16;            // EPI_BIAS_ROWADD_F32: store the output as fp16 [M][ldo] (round to nearest, saturating) instead of fp32.
+                          // The decoder's per-box k|v|q are consumed once, by fp32 FMAs, after a tf32 GEMM produced them: fp16 keeps the
+                          // same 10 explicit mantissa bits and halves their HBM traffic.
 };
 
 // Partials per row that an EPI_BIAS_RESID_STATS_F32 launch with N output columns writes to stats_out (BN = 256, two column

@@ -54,6 +54,21 @@ int make_tmap_f32_out(CUtensorMap* out, const void* base, uint64_t rows, uint64_
   return 0;
 }
 
+// fp16 row-major [rows][cols] output (GemmArgs::out_f16): the geometry of the bf16 copy below
+int make_tmap_f16_out(CUtensorMap* out, const void* base, uint64_t rows, uint64_t cols, uint64_t ld_elems) {
+  if (fetch_encode()) return set_error("cuTensorMapEncodeTiled entry point not available");
+  cuuint64_t dims[2] = {cols, rows};
+  cuuint64_t strides[1] = {ld_elems * 2};
+  cuuint32_t box[2] = {32, 32};
+  cuuint32_t estr[2] = {1, 1};
+  CUresult r = g_encode(out, CU_TENSOR_MAP_DATA_TYPE_FLOAT16, 2, const_cast<void*>(base), dims, strides, box, estr,
+                        CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_64B, CU_TENSOR_MAP_L2_PROMOTION_NONE,
+                        CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+  if (r != CUDA_SUCCESS) return set_error("cuTensorMapEncodeTiled(f16 out) failed: %d (rows=%llu cols=%llu ld=%llu)", (int)r,
+                                          (unsigned long long)rows, (unsigned long long)cols, (unsigned long long)ld_elems);
+  return 0;
+}
+
 // bf16 row-major [rows][cols] copy of the fp32 output (EPI_BIAS_RESID_STATS_F32): box = 32 columns (64 bytes) x 32 rows,
 // 64B swizzle -- the staging geometry of an fp32 half.
 int make_tmap_bf16_out(CUtensorMap* out, const void* base, uint64_t rows, uint64_t cols, uint64_t ld_elems) {
@@ -168,8 +183,9 @@ int launch_gemm(int cg, int tf32, int bn, int epi, const void* A, int lda, const
     if (make_tmap_2d(&tA, A, esz, g.M, g.K, lda, 128)) return -1;
   }
   if (make_tmap_2d(&tB, W, esz, g.N, g.K, ldw, bn / cg)) return -1;
-  CUtensorMap tO = tA;  // only the staged fp32 residual epilogue stores through a tensor map
-  if (gemm_staged(epi)) {
+  if (g.out_f16 && epi != EPI_BIAS_ROWADD_F32) return set_error("gemm: fp16 output is built for the row-add epilogue only (epi=%d)", epi);
+  CUtensorMap tO = tA;  // only the staged fp32 epilogues store through a tensor map
+  if (gemm_staged(epi) && !g.out_f16) {
     if ((reinterpret_cast<uintptr_t>(g.out) & 15) != 0 || (g.ldo * 4) % 16 != 0)
       return set_error("gemm: epilogue %d stores its fp32 output by TMA and needs a 16-byte aligned output (ldo=%d)", epi, g.ldo);
     if (make_tmap_f32_out(&tO, g.out, g.M, g.N, g.ldo)) return -1;
@@ -179,6 +195,11 @@ int launch_gemm(int cg, int tf32, int bn, int epi, const void* A, int lda, const
     if ((reinterpret_cast<uintptr_t>(g.xb_out) & 15) != 0 || (g.ldo * 2) % 16 != 0)
       return set_error("gemm: the bf16 copy needs a 16-byte aligned xb_out (ldo=%d)", g.ldo);
     if (make_tmap_bf16_out(&tX, g.xb_out, g.M, g.N, g.ldo)) return -1;
+  }
+  if (g.out_f16) {
+    if ((reinterpret_cast<uintptr_t>(g.out) & 15) != 0 || (g.ldo * 2) % 16 != 0)
+      return set_error("gemm: the fp16 output needs a 16-byte aligned out (ldo=%d)", g.ldo);
+    if (make_tmap_f16_out(&tX, g.out, g.M, g.N, g.ldo)) return -1;
   }
 
   GEMM_CASE(1, 0, 256, EPI_BIAS_BF16)

@@ -267,7 +267,7 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
     const int half = (warp - 4) >> 2;                // which share of the columns is this warp's
     int as = 0;
     uint32_t aphase = 0;
-    uint32_t sk = 0;  // EPI_BIAS_RESID_STATS_F32: running count of this warp's TMA stores (staging buffer = sk & 1)
+    uint32_t sk = 0;  // EPI_BIAS_RESID_STATS_F32 / fp16 output: running count of this warp's TMA stores (staging buffer = sk & 1)
     for (int tile = cluster_id; tile < num_tiles; tile += num_clusters) {
       const int m_blk = tile / tiles_n, n_blk = tile % tiles_n;
       const int m = m_blk * C::BM * CG + (int)rank * C::BM + q * 32 + lane;
@@ -495,7 +495,30 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
 #pragma unroll
                 for (int j = 0; j < 32; ++j) f[j] += __uint_as_float(radd[ci & 1][j]);
               }
-              stage_chunk(f, col);
+              if (EPI == EPI_BIAS_ROWADD_F32 && g.out_f16) {
+                // fp16 output: the chunk's 32 rows x 64 bytes are the geometry of one staging half (as the bf16 copy of
+                // EPI_BIAS_RESID_STATS_F32); the two halves of the warp's staging area rotate
+                uint32_t pk[16];
+#pragma unroll
+                for (int j = 0; j < 16; ++j) pk[j] = pack_f16x2_sat(f[2 * j], f[2 * j + 1]);
+                const uint32_t sbuf = staging_base + (uint32_t)(warp - 4) * 4096u;
+                const uint32_t srow = (uint32_t)lane * 64u, sx = (uint32_t)((lane >> 1) & 3);
+                if (lane == 0) bulk_wait_group_read<1>();
+                __syncwarp();
+                const uint32_t sb = sbuf + (sk++ & 1u) * 2048u;
+#pragma unroll
+                for (int j = 0; j < 4; ++j)
+                  st_shared_v4(sb + srow + (((uint32_t)j ^ sx) << 4), __uint_as_float(pk[4 * j]), __uint_as_float(pk[4 * j + 1]),
+                               __uint_as_float(pk[4 * j + 2]), __uint_as_float(pk[4 * j + 3]));
+                fence_proxy_async_smem();
+                __syncwarp();
+                if (lane == 0) {
+                  tma_store_2d(&tmX, sb, col, m - lane);
+                  bulk_commit_group();
+                }
+              } else {
+                stage_chunk(f, col);
+              }
             }
           }
         }

@@ -426,6 +426,12 @@ __device__ __forceinline__ void ld_global_v8(const void* p, uint32_t (&v)[8]) {
                : "memory");
 }
 
+// two floats -> packed fp16 (lo in the low half), round to nearest even, saturating to +-65504 instead of inf
+__device__ __forceinline__ uint32_t pack_f16x2_sat(float lo, float hi) {
+  uint32_t r;
+  asm("cvt.rn.satfinite.f16x2.f32 %0, %1, %2;" : "=r"(r) : "f"(hi), "f"(lo));
+  return r;
+}
 __device__ __forceinline__ uint32_t pack_bf16x2(float lo, float hi) {
   __nv_bfloat162 h = __floats2bfloat162_rn(lo, hi);
   return *reinterpret_cast<uint32_t*>(&h);

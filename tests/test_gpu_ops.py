@@ -197,8 +197,9 @@ def _attn_ref(q, k, v):
     return (p @ vh).transpose(-2, -3).reshape(*sh, -1, 128)
 
 
+@pytest.mark.parametrize("half", [False, True])
 @pytest.mark.parametrize("gain,shared", [(1.0, False), (1.0, True), (12.0, False), (60.0, False), (60.0, True)])
-def test_decoder_token_to_image_attention(gain, shared):
+def test_decoder_token_to_image_attention(gain, shared, half):
     """decoder_t2i_kernel against float64 torch: 7 queries x 4096 keys x 8 heads per box.  Large gains make the logits span
     thousands of log2 units with the largest keys late in each key range, so the lazy softmax shift (set by a warp's first key,
     moved when a score exceeds it by 2^24) has to move many times; `shared`: all boxes read the keys of their image."""
@@ -211,11 +212,14 @@ def test_decoder_token_to_image_attention(gain, shared):
     ramp = torch.linspace(0.2, 2.0, 4096).view(1, 4096, 1)      # later keys are larger
     kv[:, :, :128] *= ramp
     kv = kv.cuda()
+    kv_dev = kv.half() if half else kv  # fp16 storage (the engine's per-box k|v|q): the reference sees the same rounded values
+    kv = kv_dev.float()
     box_img = torch.tensor([0, 1, 1, 0, 1], dtype=torch.int32, device="cuda") if shared else None
     out = torch.full((boxes, 7, 128), float("nan"), device="cuda")
     scratch = torch.empty(int(lib.inksam_op_decoder_t2i_scratch_bytes(boxes)), dtype=torch.uint8, device="cuda")
     for _ in range(2):  # the ticket counters must be left ready for the next launch
-        _lib.check(lib.inksam_op_decoder_t2i(ptr(q), ptr(kv), 4096 * ld, ld, ptr(box_img), ptr(out), ptr(scratch), boxes, stream()))
+        _lib.check(lib.inksam_op_decoder_t2i(ptr(q), ptr(kv_dev), int(half), 4096 * ld, ld, ptr(box_img), ptr(out), ptr(scratch), boxes,
+                                             stream()))
     sel = box_img.long() if shared else torch.arange(boxes, device="cuda")
     ref = _attn_ref(q, kv[sel][:, :, :128], kv[sel][:, :, 128:256])
     assert torch.isfinite(out).all()
@@ -223,20 +227,44 @@ def test_decoder_token_to_image_attention(gain, shared):
     assert err < 2e-5, err
 
 
+@pytest.mark.parametrize("half", [False, True])
 @pytest.mark.parametrize("gain,shared", [(1.0, False), (40.0, False), (40.0, True)])
-def test_decoder_image_to_token_attention(gain, shared):
+def test_decoder_image_to_token_attention(gain, shared, half):
     """decoder_i2t_kernel against float64 torch: every image token attends to the 7 tokens."""
     lib = _lib.load()
     boxes, ld, qcol = 3, 384, 256
     g = torch.Generator().manual_seed(12)
     nimg = 2 if shared else boxes
     qsrc = (torch.randn(nimg, 4096, ld, generator=g) * gain).cuda()
+    q_dev = qsrc.half() if half else qsrc
+    qsrc = q_dev.float()
     kvt = torch.randn(boxes, 2, 7, 128, generator=g).cuda()
     box_img = torch.tensor([1, 0, 1], dtype=torch.int32, device="cuda") if shared else None
     out = torch.full((boxes * 4096, 128), float("nan"), device="cuda")
-    _lib.check(lib.inksam_op_decoder_i2t(ptr(qsrc), 4096 * ld, ld, qcol, ptr(box_img), ptr(kvt), ptr(out), boxes, stream()))
+    _lib.check(lib.inksam_op_decoder_i2t(ptr(q_dev), int(half), 4096 * ld, ld, qcol, ptr(box_img), ptr(kvt), ptr(out), boxes, stream()))
     sel = box_img.long() if shared else torch.arange(boxes, device="cuda")
     ref = _attn_ref(qsrc[sel][:, :, qcol:qcol + 128], kvt[:, 0], kvt[:, 1]).reshape(boxes * 4096, 128)
     assert torch.isfinite(out).all()
     err = (out.double() - ref).abs().max().item() / ref.abs().max().item()
     assert err < 2e-5, err
+
+
+@pytest.mark.parametrize("cg", [1, 2])
+@pytest.mark.parametrize("M,N,K,bn", [(4096 * 3, 384, 256, 128), (4096 + 77, 256, 256, 256), (300, 160, 160, 256)])
+def test_gemm_rowadd_fp16_output(cg, M, N, K, bn):
+    """The decoder's k|v|q projection (tf32 GEMM + row-add table) storing fp16: equal to the fp32-output kernel rounded to fp16
+    (round to nearest even), saturating instead of overflowing; rows beyond M untouched."""
+    from gpu_util import EPI, gemm
+    lib = _lib.load()
+    g = torch.Generator().manual_seed(5)
+    A = torch.randn(M, K, generator=g).cuda(); W = (torch.randn(N, K, generator=g) * 0.05).cuda()
+    radd = torch.randn(64, N, generator=g).cuda(); bias = torch.randn(N, generator=g).cuda()
+    radd[3, 7] = 1e6      # beyond the fp16 range: saturates to 65504
+    o32 = torch.zeros(M, N, device="cuda")
+    gemm(EPI["ROWADD"], A, W, o32, cg=cg, tf32=1, bn=bn, bias=bias, rowadd=radd, rowadd_mod=64)
+    o16 = torch.full((M + 5, N), 7.0, device="cuda", dtype=torch.float16)
+    _lib.check(lib.inksam_op_gemm_rowadd_f16(cg, 1, bn, ptr(A), K, ptr(W), K, M, N, K, ptr(o16), N, ptr(bias), ptr(radd), 64, stream()))
+    want = o32.clamp(-65504.0, 65504.0).half()
+    assert torch.equal(o16[:M], want)
+    assert (o16[M:] == 7.0).all()
+    assert o16[3, 7].item() == 65504.0
