@@ -99,7 +99,7 @@ size_t inksam_op_decoder_t2i_scratch_bytes(int boxes);
 int inksam_op_decoder_t2i(const float* q, const void* kv, int kv_half, long long box_stride, int ld, const int* box_img, float* out,
                           void* scratch, int boxes, void* stream);
 int inksam_op_decoder_i2t(const void* qsrc, int q_half, long long box_stride, int ld, int qcol, const int* box_img, const float* kv,
-                          float* out, int boxes, void* stream);
+                          void* out, int out_half, int boxes, void* stream);
 /* kv_half / q_half != 0: the k|v|q rows are fp16 (as inksam_op_gemm_rowadd_f16 writes them) instead of fp32; box_stride, ld and
  * qcol count elements either way.  The engine stores the per-box k|v|q of the decoder that way: they are written once by a tf32
  * GEMM and read once by these kernels' fp32 FMAs, and fp16 keeps the 10 explicit mantissa bits of a tf32 operand.
@@ -107,6 +107,13 @@ int inksam_op_decoder_i2t(const void* qsrc, int q_half, long long box_stride, in
  * out_f16[m][n] = fp16(acc + bias[n] + rowadd[m % rowadd_mod][n]), round to nearest, saturating at +-65504. */
 int inksam_op_gemm_rowadd_f16(int cg, int tf32, int bn, const void* A, int lda, const void* W, int ldw, int M, int N, int K,
                               void* out_f16, int ldo, const float* bias, const float* rowadd, int rowadd_mod, void* stream);
+/* out_half != 0 (inksam_op_decoder_i2t): the attention output is stored as fp16 [boxes*4096][128].
+ * inksam_op_gemm_f16: inksam_op_gemm with fp16 operands A [M][lda] and W [N][ldw] (kind::f16 MMAs, fp32 accumulation) for the
+ * epilogues the decoder's fp16 intermediates go through -- epi 3 (row-add), 6 (residual + LayerNorm, N == bn == 256),
+ * 8 (upscale 1, bn 256), 9 (upscale 2 + mask, bn 128); out_f16 != 0 stores the output as fp16 (epi 3, 6, 8). */
+int inksam_op_gemm_f16(int cg, int bn, int epi, const void* A, int lda, const void* W, int ldw, int M, int N, int K, void* out, int ldo,
+                       int out_f16, const float* bias, const float* resid, const float* rowadd, int rowadd_mod, const float* ln_w,
+                       const float* ln_b, float ln_eps, const float* hyper, int resid_mod, void* stream);
 
 /* ResizeLongestSide.apply_image on the device: Pillow's 8-bit bilinear resample (torchvision resize of a PIL image,
  * SA/utils/transforms.py:26-31; algorithm of Pillow libImaging/Resample.c), bit-exact with the host path.

@@ -35,6 +35,16 @@ int inksam_op_gemm_rowadd_f16(int cg, int tf32, int bn, const void* A, int lda, 
   return launch_gemm(cg, tf32, bn, EPI_BIAS_ROWADD_F32, A, lda, W, ldw, g, device_sms(), static_cast<cudaStream_t>(stream));
 }
 
+int inksam_op_gemm_f16(int cg, int bn, int epi, const void* A, int lda, const void* W, int ldw, int M, int N, int K, void* out, int ldo,
+                       int out_f16, const float* bias, const float* resid, const float* rowadd, int rowadd_mod, const float* ln_w,
+                       const float* ln_b, float ln_eps, const float* hyper, int resid_mod, void* stream) {
+  GemmArgs g{};
+  g.M = M; g.N = N; g.K = K; g.ldo = ldo; g.out = out; g.bias = bias; g.resid = resid; g.rowadd = rowadd; g.rowadd_mod = rowadd_mod;
+  g.ln_w = ln_w; g.ln_b = ln_b; g.ln_eps = ln_eps; g.hyper = hyper; g.resid_mod = resid_mod;
+  g.ab_f16 = 1; g.out_f16 = out_f16;
+  return launch_gemm(cg, 0, bn, epi, A, lda, W, ldw, g, device_sms(), static_cast<cudaStream_t>(stream));
+}
+
 int inksam_op_attention(int windowed, const void* qkv, const void* rel, void* out, int B, int heads, int head_dim, void* stream) {
   return launch_attention(windowed, qkv, rel, out, B, heads, head_dim, static_cast<cudaStream_t>(stream));
 }
@@ -96,11 +106,11 @@ int inksam_op_decoder_t2i(const float* q, const void* kv, int kv_half, long long
 }
 
 int inksam_op_decoder_i2t(const void* qsrc, int q_half, long long box_stride, int ld, int qcol, const int* box_img, const float* kv,
-                          float* out, int boxes, void* stream) {
+                          void* out, int out_half, int boxes, void* stream) {
   if (!qsrc || !kv || !out || boxes < 1) return set_error("inksam_op_decoder_i2t: null argument or no boxes");
   if (ld % 4 != 0 || qcol % 4 != 0 || qcol + 128 > ld || (reinterpret_cast<uintptr_t>(qsrc) & 15) != 0 || box_stride % 4 != 0)
     return set_error("inksam_op_decoder_i2t: q rows must be 16-byte aligned (ld=%d qcol=%d)", ld, qcol);
-  return launch_decoder_i2t(qsrc, q_half, box_stride, ld, qcol, box_img, kv, out, boxes, static_cast<cudaStream_t>(stream));
+  return launch_decoder_i2t(qsrc, q_half, box_stride, ld, qcol, box_img, kv, out, out_half, boxes, static_cast<cudaStream_t>(stream));
 }
 
 int inksam_op_patchify(const void* images, int dtype, int B, const int* hw, long long img_stride, long long row_pitch,

@@ -506,10 +506,10 @@ size_t decoder_t2i_scratch_floats(int boxes) { return (size_t)boxes * T2I_SPLITS
 // 16-byte access per lane, and the four partial dot products of a head meet through two shuffles.
 constexpr int I2T_PIX = 512;  // pixels per block
 
-template <bool HALF>
+template <bool HALF, bool OUT_HALF>
 __global__ void __launch_bounds__(256) decoder_i2t_kernel(const void* __restrict__ qsrc, long long box_stride, int ld, int qcol,
                                                           const int* __restrict__ box_img, const float* __restrict__ kv,
-                                                          float* __restrict__ out) {
+                                                          void* __restrict__ out) {
   constexpr int ES = HALF ? 2 : 4;
   const int box = blockIdx.y, tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
   // lane = head * 4 + quarter = float4 index inside the 128-float row
@@ -526,7 +526,8 @@ __global__ void __launch_bounds__(256) decoder_i2t_kernel(const void* __restrict
   }
   const char* qbase = static_cast<const char*>(qsrc) + ((size_t)(box_img ? box_img[box] : box) * box_stride + qcol) * ES;
   const int pix0 = blockIdx.x * I2T_PIX + warp;
-  float4* obase = reinterpret_cast<float4*>(out + (size_t)box * 4096 * 128);
+  // out: [box*4096][128] fp32, or fp16 when the out_proj GEMM that consumes it takes fp16 operands (GemmArgs::ab_f16)
+  char* obase = static_cast<char*>(out) + (size_t)box * 4096 * 128 * (OUT_HALF ? 2 : 4);
   constexpr int NP = I2T_PIX / 8;  // pixels per warp
   constexpr int PD = Row4<HALF>::DEPTH;
   typename Row4<HALF>::Raw qn[PD];
@@ -556,14 +557,23 @@ __global__ void __launch_bounds__(256) decoder_i2t_kernel(const void* __restrict
       const float p = sc[t] * inv;
       o.x += p * v4[t].x; o.y += p * v4[t].y; o.z += p * v4[t].z; o.w += p * v4[t].w;
     }
-    obase[(size_t)pix * 32 + lane] = o;
+    if constexpr (OUT_HALF) {
+      uint2 h2;
+      h2.x = pack_f16x2_sat(o.x, o.y); h2.y = pack_f16x2_sat(o.z, o.w);
+      reinterpret_cast<uint2*>(obase)[(size_t)pix * 32 + lane] = h2;
+    } else {
+      reinterpret_cast<float4*>(obase)[(size_t)pix * 32 + lane] = o;
+    }
   }
 }
 
 int launch_decoder_i2t(const void* qsrc, int q_half, long long box_stride, int ld, int qcol, const int* box_img, const float* kv,
-                       float* out, int boxes, cudaStream_t st) {
-  if (q_half) decoder_i2t_kernel<true><<<dim3(4096 / I2T_PIX, boxes), 256, 0, st>>>(qsrc, box_stride, ld, qcol, box_img, kv, out);
-  else decoder_i2t_kernel<false><<<dim3(4096 / I2T_PIX, boxes), 256, 0, st>>>(qsrc, box_stride, ld, qcol, box_img, kv, out);
+                       void* out, int out_half, int boxes, cudaStream_t st) {
+  const dim3 grid(4096 / I2T_PIX, boxes);
+  if (q_half && out_half) decoder_i2t_kernel<true, true><<<grid, 256, 0, st>>>(qsrc, box_stride, ld, qcol, box_img, kv, out);
+  else if (q_half) decoder_i2t_kernel<true, false><<<grid, 256, 0, st>>>(qsrc, box_stride, ld, qcol, box_img, kv, out);
+  else if (out_half) decoder_i2t_kernel<false, true><<<grid, 256, 0, st>>>(qsrc, box_stride, ld, qcol, box_img, kv, out);
+  else decoder_i2t_kernel<false, false><<<grid, 256, 0, st>>>(qsrc, box_stride, ld, qcol, box_img, kv, out);
   CUDA_TRY(cudaGetLastError());
   return 0;
 }

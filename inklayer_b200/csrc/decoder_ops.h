@@ -50,7 +50,7 @@ int launch_decoder_t2i(const float* q, const void* kv, int kv_half, long long bo
                        float* partial, int* ticket, int boxes, cudaStream_t st);
 size_t decoder_t2i_scratch_floats(int boxes);  // floats of `partial`; `ticket` is `boxes` ints, zeroed once
 int launch_decoder_i2t(const void* qsrc, int q_half, long long box_stride, int ld, int qcol, const int* box_img, const float* kv,
-                       float* out, int boxes, cudaStream_t st);
+                       void* out, int out_half, int boxes, cudaStream_t st);
 int launch_decoder_keys0(const float* emb, const float* nomask, float* keys, int B, cudaStream_t st);
 int launch_box_image_index(const BoxSegments& seg, int* box_img, cudaStream_t st);
 int launch_dense_pe(const float* gauss, float* pe, cudaStream_t st);

@@ -1,5 +1,6 @@
 // HBM-bound helper kernels of the image encoder: pixel normalisation + patch gather, LayerNorm -> bf16,
 // fp32 -> bf16 cast, and the bias rows of padded window tokens.
+#include <cuda_fp16.h>
 #include "common.h"
 #include "ptx.cuh"
 
@@ -267,7 +268,8 @@ __global__ void __launch_bounds__(256) repack_kernel(const RepackArgs a) {
       src += c * a.istride_of_odim[d];
     }
     const float v = a.in[src];
-    if (a.out_bf16) static_cast<__nv_bfloat16*>(a.out)[i] = __float2bfloat16_rn(v);
+    if (a.out_bf16 == 1) static_cast<__nv_bfloat16*>(a.out)[i] = __float2bfloat16_rn(v);
+    else if (a.out_bf16 == 2) static_cast<__half*>(a.out)[i] = __float2half_rn(v);  // (decoder weights: |w| far below 65504)
     else static_cast<float*>(a.out)[i] = v;
   }
 }

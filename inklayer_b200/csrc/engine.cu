@@ -45,6 +45,9 @@ struct inksam_handle {
   float *pe = nullptr;                       // dense PE, token-major [4096][256]
   float *wkvq[2] = {nullptr, nullptr}, *bkvq[2] = {nullptr, nullptr}, *ra[2] = {nullptr, nullptr};  // [384][256], [384], [4096][384]
   float *wkvf = nullptr, *bkvf = nullptr, *raf = nullptr;                                            // [256][256], [256], [4096][256]
+  // fp16 copies of the weights whose A operand is an fp16 intermediate (GemmArgs::ab_f16): out_proj of the two image->token
+  // attentions [256][128], the final k|v projection [256][256], the two transposed convolutions [256][256] / [128][64]
+  void *wo16[2] = {nullptr, nullptr}, *wkvf16 = nullptr, *up0_16 = nullptr, *up3_16 = nullptr;
   // workspaces: sized once by inksam_reserve, otherwise grow-only.  A buffer that has to grow is RETIRED, not freed (work
   // already enqueued on any stream -- or baked into a captured CUDA graph -- may still use it); retired buffers are released
   // by inksam_reserve / inksam_destroy after a device synchronisation.  ws_generation counts reallocations so that the
@@ -349,6 +352,26 @@ int finalize_decoder(inksam_handle* h, cudaStream_t st) {
     if (fin) { h->wkvf = wm; h->bkvf = bm; h->raf = ra; }
     else { h->wkvq[l] = wm; h->bkvq[l] = bm; h->ra[l] = ra; }
   }
+  // fp16 copies (see inksam_handle)
+  auto to_f16 = [&](const float* src, long long rows, long long cols, void** out) -> int {
+    INK_TRY(dev_alloc(h, out, (size_t)rows * cols * 2));
+    const long long shp[2] = {rows, cols};
+    ++h->launches;
+    return launch_repack(src, *out, 2, shp, 2, nullptr, st);
+  };
+  for (int l = 0; l < 2; ++l) {
+    const float* ow;
+    INK_TRY(need_f32(h, T + "layers." + std::to_string(l) + ".cross_attn_image_to_token.out_proj.weight", &ow));
+    INK_TRY(to_f16(ow, 256, 128, &h->wo16[l]));
+  }
+  INK_TRY(to_f16(h->wkvf, 256, 256, &h->wkvf16));
+  {
+    const float *u0w, *u3w;
+    INK_TRY(need_f32(h, "mask_decoder.output_upscaling.0.weight", &u0w));
+    INK_TRY(need_f32(h, "mask_decoder.output_upscaling.3.weight", &u3w));
+    INK_TRY(to_f16(u0w, 256, 256, &h->up0_16));
+    INK_TRY(to_f16(u3w, 128, 64, &h->up3_16));
+  }
   return 0;
 }
 
@@ -612,19 +635,21 @@ int decode_chunk(inksam_handle* h, const float* keys0, const float* kvq0, char* 
     ++h->launches;
     return launch_decoder_t2i(s.q_t2i, kv, half, stride, ld, bi, s.attn_t2i, t2i_part, t2i_ticket, n, st);
   };
+  // ... and so are the GEMM-to-GEMM intermediates: the image->token attention output a1 (A of out_proj), the final keys
+  // (A of the final k|v projection and of the first transposed convolution) and that convolution's output (A of the second)
   auto i2t = [&](const void* q, int half, long long stride, const int* bi) {
     ++h->launches;
-    return launch_decoder_i2t(q, half, stride, 384, 256, bi, s.kv_i2t, a1, n, st);
+    return launch_decoder_i2t(q, half, stride, 384, 256, bi, s.kv_i2t, a1, 1, n, st);
   };
   // keys <- norm4(keys + out_proj(image->token attention))   (transformer.py:176-180)
-  auto keys_update = [&](int layer, const float* resid, int resid_mod, const int* row_img) -> int {
-    const float *ow, *ob, *nw, *nb;
-    INK_TRY(need_f32(h, T + std::to_string(layer) + ".cross_attn_image_to_token.out_proj.weight", &ow));
+  auto keys_update = [&](int layer, const float* resid, int resid_mod, const int* row_img, void* out, int out_f16) -> int {
+    const float *ob, *nw, *nb;
     INK_TRY(need_f32(h, T + std::to_string(layer) + ".cross_attn_image_to_token.out_proj.bias", &ob));
     INK_TRY(need_f32(h, T + std::to_string(layer) + ".norm4.weight", &nw));
     INK_TRY(need_f32(h, T + std::to_string(layer) + ".norm4.bias", &nb));
-    G c; c.tf32 = 1; c.epi = EPI_RESID_LN_F32; c.A = a1; c.lda = 128; c.W = ow; c.ldw = 128;
-    c.g.M = Mb; c.g.N = 256; c.g.K = 128; c.g.ldo = 256; c.g.out = keysb; c.g.bias = ob; c.g.resid = resid;
+    G c; c.tf32 = 0; c.epi = EPI_RESID_LN_F32; c.A = a1; c.lda = 128; c.W = h->wo16[layer]; c.ldw = 128;
+    c.g.ab_f16 = 1; c.g.out_f16 = out_f16;
+    c.g.M = Mb; c.g.N = 256; c.g.K = 128; c.g.ldo = 256; c.g.out = out; c.g.bias = ob; c.g.resid = resid;
     c.g.resid_mod = resid_mod; c.g.row_img = row_img; c.g.ln_w = nw; c.g.ln_b = nb; c.g.ln_eps = 1e-5f;
     return run_gemm(h, c, st);
   };
@@ -634,7 +659,7 @@ int decode_chunk(inksam_handle* h, const float* keys0, const float* kvq0, char* 
   INK_TRY(t2i(kvq0, 0, 4096LL * 384, 384, bimg));
   INK_TRY(tokens(2, 0));
   INK_TRY(i2t(kvq0, 0, 4096LL * 384, bimg));
-  INK_TRY(keys_update(0, keys0, 4096, bimg));
+  INK_TRY(keys_update(0, keys0, 4096, bimg, keysb, 0));
   // ---- layer 1: per-box keys
   {
     G c; c.tf32 = 1; c.bn = 128; c.epi = EPI_BIAS_ROWADD_F32; c.A = keysb; c.lda = 256; c.W = h->wkvq[1]; c.ldw = 256;
@@ -646,12 +671,15 @@ int decode_chunk(inksam_handle* h, const float* keys0, const float* kvq0, char* 
   INK_TRY(t2i(kvq, 1, 4096LL * 384, 384, nullptr));
   INK_TRY(tokens(2, 1));
   INK_TRY(i2t(kvq, 1, 4096LL * 384, nullptr));
-  INK_TRY(keys_update(1, keysb, 0, nullptr));
+  // the final keys are fp16 only: [n][4096][256] halves in the upper half of the k|v|q buffer (layer 1's k|v|q are dead; the
+  // final k|v and then the upscaled map go into its lower part)
+  void* keys2 = reinterpret_cast<char*>(kvq) + (size_t)n * 4096 * 384 * 2;
+  INK_TRY(keys_update(1, keysb, 0, nullptr, keys2, 1));
   // ---- final token -> image attention
   {
-    G c; c.tf32 = 1; c.epi = EPI_BIAS_ROWADD_F32; c.A = keysb; c.lda = 256; c.W = h->wkvf; c.ldw = 256;
+    G c; c.tf32 = 0; c.epi = EPI_BIAS_ROWADD_F32; c.A = keys2; c.lda = 256; c.W = h->wkvf16; c.ldw = 256;
     c.g.M = Mb; c.g.N = 256; c.g.K = 256; c.g.ldo = 256; c.g.out = kvq; c.g.bias = nullptr; c.g.rowadd = h->raf;
-    c.g.rowadd_mod = 4096; c.g.out_f16 = 1;
+    c.g.rowadd_mod = 4096; c.g.out_f16 = 1; c.g.ab_f16 = 1;
     INK_TRY(run_gemm(h, c, st));
   }
   INK_TRY(tokens(3, 0));
@@ -665,16 +693,17 @@ int decode_chunk(inksam_handle* h, const float* keys0, const float* kvq0, char* 
   INK_TRY(need_f32(h, "mask_decoder.output_upscaling.1.bias", &u1b));
   INK_TRY(need_f32(h, "mask_decoder.output_upscaling.3.weight", &u3w));
   INK_TRY(need_f32(h, "mask_decoder.output_upscaling.3.bias", &u3b));
-  float* up1 = kvq;  // [n][128][128][64]
+  void* up1 = kvq;  // [n][128][128][64] fp16 (the final k|v there are dead)
   {
-    G c; c.tf32 = 1; c.epi = EPI_UPSCALE1; c.A = keysb; c.lda = 256; c.W = u0w; c.ldw = 256;
+    G c; c.tf32 = 0; c.epi = EPI_UPSCALE1; c.A = keys2; c.lda = 256; c.W = h->up0_16; c.ldw = 256;
     c.g.M = Mb; c.g.N = 256; c.g.K = 256; c.g.ldo = 256; c.g.out = up1; c.g.bias = u0b; c.g.ln_w = u1w; c.g.ln_b = u1b;
-    c.g.ln_eps = 1e-6f;
+    c.g.ln_eps = 1e-6f; c.g.ab_f16 = 1; c.g.out_f16 = 1;
     INK_TRY(run_gemm(h, c, st));
   }
   {
-    G c; c.tf32 = 1; c.bn = 128; c.epi = EPI_UPSCALE2_MASK; c.A = up1; c.lda = 64; c.W = u3w; c.ldw = 64;
+    G c; c.tf32 = 0; c.bn = 128; c.epi = EPI_UPSCALE2_MASK; c.A = up1; c.lda = 64; c.W = h->up3_16; c.ldw = 64;
     c.g.M = n * 16384; c.g.N = 128; c.g.K = 64; c.g.ldo = 128; c.g.out = low; c.g.bias = u3b; c.g.hyper = s.hyper;
+    c.g.ab_f16 = 1;
     INK_TRY(run_gemm(h, c, st));
   }
   // ---- fused upsample + crop + resize + threshold: one launch for every box of the chunk (a segment per image)

@@ -183,7 +183,9 @@ int launch_gemm(int cg, int tf32, int bn, int epi, const void* A, int lda, const
     if (make_tmap_2d(&tA, A, esz, g.M, g.K, lda, 128)) return -1;
   }
   if (make_tmap_2d(&tB, W, esz, g.N, g.K, ldw, bn / cg)) return -1;
-  if (g.out_f16 && epi != EPI_BIAS_ROWADD_F32) return set_error("gemm: fp16 output is built for the row-add epilogue only (epi=%d)", epi);
+  if (g.out_f16 && epi != EPI_BIAS_ROWADD_F32 && epi != EPI_RESID_LN_F32 && epi != EPI_UPSCALE1)
+    return set_error("gemm: fp16 output is built for the row-add, residual + LayerNorm and upscale-1 epilogues only (epi=%d)", epi);
+  if (g.ab_f16 && tf32) return set_error("gemm: fp16 operands go with tf32 = 0");
   CUtensorMap tO = tA;  // only the staged fp32 epilogues store through a tensor map
   if (gemm_staged(epi) && !g.out_f16) {
     if ((reinterpret_cast<uintptr_t>(g.out) & 15) != 0 || (g.ldo * 4) % 16 != 0)
@@ -196,7 +198,7 @@ int launch_gemm(int cg, int tf32, int bn, int epi, const void* A, int lda, const
       return set_error("gemm: the bf16 copy needs a 16-byte aligned xb_out (ldo=%d)", g.ldo);
     if (make_tmap_bf16_out(&tX, g.xb_out, g.M, g.N, g.ldo)) return -1;
   }
-  if (g.out_f16) {
+  if (g.out_f16 && epi != EPI_UPSCALE1) {
     if ((reinterpret_cast<uintptr_t>(g.out) & 15) != 0 || (g.ldo * 2) % 16 != 0)
       return set_error("gemm: the fp16 output needs a 16-byte aligned out (ldo=%d)", g.ldo);
     if (make_tmap_f16_out(&tX, g.out, g.M, g.N, g.ldo)) return -1;
@@ -234,6 +236,10 @@ int launch_gemm(int cg, int tf32, int bn, int epi, const void* A, int lda, const
   GEMM_CASE(2, 1, 128, EPI_BIAS_ROWADD_F32)
   GEMM_CASE(1, 1, 128, EPI_UPSCALE2_MASK)
   GEMM_CASE(2, 1, 128, EPI_UPSCALE2_MASK)
+  // 2-byte operands with the decoder's epilogues: fp16 GEMM-to-GEMM intermediates (GemmArgs::ab_f16)
+  GEMM_CASE(2, 0, 256, EPI_RESID_LN_F32)
+  GEMM_CASE(2, 0, 256, EPI_UPSCALE1)
+  GEMM_CASE(2, 0, 128, EPI_UPSCALE2_MASK)
   return set_error("gemm: no kernel for cg=%d tf32=%d bn=%d epi=%d", cg, tf32, bn, epi);
 }
 

@@ -239,6 +239,7 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
       uint32_t phase = 0;
       int as = 0;
       uint32_t aphase = 0;
+      const uint32_t idesc = (!TF32 && g.ab_f16) ? make_idesc(0u, C::BM * CG, BN) : C::IDESC;  // fp16 operands: formats 0
       for (int tile = cluster_id; tile < num_tiles; tile += num_clusters) {
         mbar_wait_cluster(tempty_bar(as), aphase ^ 1u);  // epilogue has drained this accumulator
         tc_fence_after();
@@ -251,7 +252,7 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
           const uint64_t bdesc = make_kmajor_sw128_desc(a_addr + C::A_BYTES);
 #pragma unroll
           for (int k = 0; k < 4; ++k)  // 4 x 32 bytes of K per 128-byte swizzled row
-            umma<CG, TF32>(d_tmem, adesc + 2u * k, bdesc + 2u * k, C::IDESC, (uint32_t)((kb | k) != 0));
+            umma<CG, TF32>(d_tmem, adesc + 2u * k, bdesc + 2u * k, idesc, (uint32_t)((kb | k) != 0));
           umma_commit<CG>(empty_bar(stage));  // smem slot free once these MMAs retire
           if (++stage == C::STAGES) { stage = 0; phase ^= 1u; }
         }
@@ -351,6 +352,29 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
             tma_store_2d(&tmO, sb, col + hf * 16, m - lane);
             bulk_commit_group();
           }
+        }
+      };
+
+      // the same for an fp16 output: the chunk's 32 rows x 64 bytes are the geometry of ONE staging half (as the bf16 copy of
+      // EPI_BIAS_RESID_STATS_F32, tensor map tmX); the two halves of the warp's staging area rotate (sk)
+      [[maybe_unused]] auto stage_chunk_f16 = [&](const float* x, int col) {
+        uint32_t pk[16];
+#pragma unroll
+        for (int j = 0; j < 16; ++j) pk[j] = pack_f16x2_sat(x[2 * j], x[2 * j + 1]);
+        const uint32_t sbuf = staging_base + (uint32_t)(warp - 4) * 4096u;
+        const uint32_t srow = (uint32_t)lane * 64u, sx = (uint32_t)((lane >> 1) & 3);
+        if (lane == 0) bulk_wait_group_read<1>();
+        __syncwarp();
+        const uint32_t sb = sbuf + (sk++ & 1u) * 2048u;
+#pragma unroll
+        for (int j = 0; j < 4; ++j)
+          st_shared_v4(sb + srow + (((uint32_t)j ^ sx) << 4), __uint_as_float(pk[4 * j]), __uint_as_float(pk[4 * j + 1]),
+                       __uint_as_float(pk[4 * j + 2]), __uint_as_float(pk[4 * j + 3]));
+        fence_proxy_async_smem();
+        __syncwarp();
+        if (lane == 0) {
+          tma_store_2d(&tmX, sb, col, m - lane);
+          bulk_commit_group();
         }
       };
 
@@ -496,26 +520,7 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
                 for (int j = 0; j < 32; ++j) f[j] += __uint_as_float(radd[ci & 1][j]);
               }
               if (EPI == EPI_BIAS_ROWADD_F32 && g.out_f16) {
-                // fp16 output: the chunk's 32 rows x 64 bytes are the geometry of one staging half (as the bf16 copy of
-                // EPI_BIAS_RESID_STATS_F32); the two halves of the warp's staging area rotate
-                uint32_t pk[16];
-#pragma unroll
-                for (int j = 0; j < 16; ++j) pk[j] = pack_f16x2_sat(f[2 * j], f[2 * j + 1]);
-                const uint32_t sbuf = staging_base + (uint32_t)(warp - 4) * 4096u;
-                const uint32_t srow = (uint32_t)lane * 64u, sx = (uint32_t)((lane >> 1) & 3);
-                if (lane == 0) bulk_wait_group_read<1>();
-                __syncwarp();
-                const uint32_t sb = sbuf + (sk++ & 1u) * 2048u;
-#pragma unroll
-                for (int j = 0; j < 4; ++j)
-                  st_shared_v4(sb + srow + (((uint32_t)j ^ sx) << 4), __uint_as_float(pk[4 * j]), __uint_as_float(pk[4 * j + 1]),
-                               __uint_as_float(pk[4 * j + 2]), __uint_as_float(pk[4 * j + 3]));
-                fence_proxy_async_smem();
-                __syncwarp();
-                if (lane == 0) {
-                  tma_store_2d(&tmX, sb, col, m - lane);
-                  bulk_commit_group();
-                }
+                stage_chunk_f16(f, col);
               } else {
                 stage_chunk(f, col);
               }
@@ -579,7 +584,7 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
             f[h * 4 + 2] = (f[h * 4 + 2] - mean) * rstd * w0.z + b0.z;
             f[h * 4 + 3] = (f[h * 4 + 3] - mean) * rstd * w0.w + b0.w;
           }
-          stage_chunk(f, c * 32);
+          if (g.out_f16) stage_chunk_f16(f, c * 32); else stage_chunk(f, c * 32);
         }
       } else if constexpr (EPI == EPI_LN_BF16_PAD || EPI == EPI_LN_F32_NCHW) {
         // LayerNorm over the N == BN columns of this thread's row; the row lives in TMEM, so the three
@@ -704,7 +709,20 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
             f1[j + 2] = gelu_erf((f1[j + 2] - mean) * rstd * w1.z + c1.z);
             f1[j + 3] = gelu_erf((f1[j + 3] - mean) * rstd * w1.w + c1.w);
           }
-          if (row_ok) {
+          if (row_ok && g.out_f16) {  // 64 channels = 128 contiguous bytes per sub-pixel
+            const int Y = 2 * y + (sp >> 1), X = 2 * x + (sp & 1);
+            uint32_t* o = reinterpret_cast<uint32_t*>(g.out) + (((size_t)bx * 128 + Y) * 128 + X) * 32;
+#pragma unroll
+            for (int h = 0; h < 2; ++h) {
+              uint32_t pk[8];
+#pragma unroll
+              for (int j = 0; j < 8; ++j) pk[j] = pack_f16x2_sat(f0[h * 16 + 2 * j], f0[h * 16 + 2 * j + 1]);
+              st_global_v8(o + h * 8, pk);
+#pragma unroll
+              for (int j = 0; j < 8; ++j) pk[j] = pack_f16x2_sat(f1[h * 16 + 2 * j], f1[h * 16 + 2 * j + 1]);
+              st_global_v8(o + 16 + h * 8, pk);
+            }
+          } else if (row_ok) {
             const int Y = 2 * y + (sp >> 1), X = 2 * x + (sp & 1);
             float* o = reinterpret_cast<float*>(g.out) + (((size_t)bx * 128 + Y) * 128 + X) * 64;
 #pragma unroll

@@ -120,3 +120,70 @@ def test_upscale_epilogues(cg):
     u = F.gelu(F.conv_transpose2d(ref1.permute(0, 3, 1, 2), ct3, b3, stride=2))  # [n,32,256,256]
     ref2 = torch.einsum("nc,nchw->nhw", hyper, u)
     assert rel_err(low, ref2) < 3e-3
+
+
+def gemm_f16(epi, A, W, out, bn=256, out_f16=0, bias=None, resid=None, rowadd=None, rowadd_mod=1, ln_w=None, ln_b=None, eps=1e-6,
+             hyper=None, resid_mod=0):
+    import ctypes
+    from gpu_util import ptr, stream
+    from inklayer_b200 import _lib
+    M, K = A.shape
+    N = W.shape[0]
+    ldo = N
+    _lib.check(_lib.load().inksam_op_gemm_f16(2, bn, epi, ptr(A), A.stride(0), ptr(W), W.stride(0), M, N, K, ptr(out), ldo, out_f16,
+                                              ptr(bias), ptr(resid), ptr(rowadd), rowadd_mod, ptr(ln_w), ptr(ln_b), ctypes.c_float(eps),
+                                              ptr(hyper), resid_mod, stream()))
+
+
+def test_fp16_operand_decoder_epilogues():
+    """The decoder's GEMM-to-GEMM intermediates are stored as fp16 (GemmArgs::ab_f16 / out_f16): the same epilogues as
+    test_tf32_decoder_epilogues / test_upscale_epilogues with fp16 A and W (exact products, fp32 accumulation: against torch
+    fp32 on the SAME fp16-rounded operands the error is accumulation order only) and fp16 outputs (one rounding, 2^-11)."""
+    torch.backends.cuda.matmul.allow_tf32 = False
+    n = 2
+    M = n * 4096
+    # final k|v projection: A = the final keys (fp16), row-add table, fp16 output
+    A = rnd(M, 256, seed=1).half(); W = rnd(256, 256, scale=0.06, seed=2).half(); radd = rnd(4096, 256, seed=4)
+    o16 = torch.zeros(M, 256, device="cuda", dtype=torch.float16)
+    gemm_f16(EPI["ROWADD"], A, W, o16, out_f16=1, rowadd=radd, rowadd_mod=4096)
+    ref = A.float() @ W.float().t() + radd.repeat(n, 1)
+    assert rel_err(o16, ref) < 6e-4
+    # keys <- LayerNorm(keys + out_proj(a) + b): fp16 attention output and weight, fp32 residual; fp32 and fp16 outputs
+    a1 = rnd(M, 128, seed=5).half(); wo = rnd(256, 128, scale=0.08, seed=6).half(); bo = rnd(256, seed=7)
+    keys0 = rnd(4096, 256, seed=8); lw = 1 + 0.1 * rnd(256, seed=9); lb = 0.1 * rnd(256, seed=10)
+    keys = torch.zeros(M, 256, device="cuda")
+    gemm_f16(EPI["RESID_LN"], a1, wo, keys, bias=bo, resid=keys0, resid_mod=4096, ln_w=lw, ln_b=lb, eps=1e-5)
+    ref = F.layer_norm(keys0.repeat(n, 1) + a1.float() @ wo.float().t() + bo, (256,), lw, lb, 1e-5)
+    assert rel_err(keys, ref) < 2e-5
+    k16 = torch.zeros(M, 256, device="cuda", dtype=torch.float16)
+    gemm_f16(EPI["RESID_LN"], a1, wo, k16, out_f16=1, bias=bo, resid=ref, ln_w=lw, ln_b=lb, eps=1e-5)
+    ref2 = F.layer_norm(ref + a1.float() @ wo.float().t() + bo, (256,), lw, lb, 1e-5)
+    assert rel_err(k16, ref2) < 6e-4
+    assert torch.equal(k16, _same_as_fp32_then_half(a1, wo, bo, ref, lw, lb))
+    # the two transposed convolutions
+    keysh = rnd(M, 256, seed=11).half()
+    ct0 = rnd(256, 64, 2, 2, scale=0.06, seed=12); b0 = rnd(64, seed=13)
+    lw0 = 1 + 0.1 * rnd(64, seed=14); lb0 = 0.1 * rnd(64, seed=15)
+    w0 = ct0.permute(2, 3, 1, 0).reshape(256, 256).contiguous().half()
+    up1 = torch.zeros(n, 128, 128, 64, device="cuda", dtype=torch.float16)
+    gemm_f16(EPI["UPSCALE1"], keysh, w0, up1, out_f16=1, bias=b0, ln_w=lw0, ln_b=lb0, eps=1e-6)
+    ct0h = w0.float().reshape(2, 2, 64, 256).permute(3, 2, 0, 1).contiguous()
+    x = keysh.float().reshape(n, 64, 64, 256).permute(0, 3, 1, 2)
+    r = F.conv_transpose2d(x, ct0h, b0, stride=2).permute(0, 2, 3, 1)
+    ref1 = F.gelu(F.layer_norm(r, (64,), lw0, lb0, 1e-6))
+    assert rel_err(up1, ref1) < 8e-4
+    ct3 = rnd(64, 32, 2, 2, scale=0.1, seed=16); b3 = rnd(32, seed=17); hyper = rnd(n, 32, seed=18)
+    w3 = ct3.permute(2, 3, 1, 0).reshape(128, 64).contiguous().half()
+    low = torch.zeros(n, 256, 256, device="cuda")
+    gemm_f16(EPI["UPSCALE2"], up1.reshape(n * 16384, 64), w3, low, bn=128, bias=b3, hyper=hyper)
+    ct3h = w3.float().reshape(2, 2, 32, 64).permute(3, 2, 0, 1).contiguous()
+    u = F.gelu(F.conv_transpose2d(up1.float().permute(0, 3, 1, 2), ct3h, b3, stride=2))
+    ref3 = torch.einsum("nc,nchw->nhw", hyper, u)
+    assert rel_err(low, ref3) < 3e-5
+
+
+def _same_as_fp32_then_half(a1, wo, bo, resid, lw, lb):
+    """The fp16-output kernel must equal the fp32-output kernel rounded to fp16."""
+    k32 = torch.zeros(a1.shape[0], 256, device="cuda")
+    gemm_f16(EPI["RESID_LN"], a1, wo, k32, bias=bo, resid=resid, ln_w=lw, ln_b=lb, eps=1e-5)
+    return k32.half()
