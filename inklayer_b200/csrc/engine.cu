@@ -47,7 +47,7 @@ struct inksam_handle {
   float *wkvf = nullptr, *bkvf = nullptr, *raf = nullptr;                                            // [256][256], [256], [4096][256]
   // fp16 copies of the weights whose A operand is an fp16 intermediate (GemmArgs::ab_f16): out_proj of the two image->token
   // attentions [256][128], the final k|v projection [256][256], the two transposed convolutions [256][256] / [128][64]
-  void *wo16[2] = {nullptr, nullptr}, *wkvf16 = nullptr, *up0_16 = nullptr, *up3_16 = nullptr;
+  void *wo16[2] = {nullptr, nullptr}, *wkvq16 = nullptr, *wkvf16 = nullptr, *up0_16 = nullptr, *up3_16 = nullptr;
   // workspaces: sized once by inksam_reserve, otherwise grow-only.  A buffer that has to grow is RETIRED, not freed (work
   // already enqueued on any stream -- or baked into a captured CUDA graph -- may still use it); retired buffers are released
   // by inksam_reserve / inksam_destroy after a device synchronisation.  ws_generation counts reallocations so that the
@@ -364,6 +364,7 @@ int finalize_decoder(inksam_handle* h, cudaStream_t st) {
     INK_TRY(need_f32(h, T + "layers." + std::to_string(l) + ".cross_attn_image_to_token.out_proj.weight", &ow));
     INK_TRY(to_f16(ow, 256, 128, &h->wo16[l]));
   }
+  INK_TRY(to_f16(h->wkvq[1], 384, 256, &h->wkvq16));
   INK_TRY(to_f16(h->wkvf, 256, 256, &h->wkvf16));
   {
     const float *u0w, *u3w;
@@ -642,14 +643,15 @@ int decode_chunk(inksam_handle* h, const float* keys0, const float* kvq0, char* 
     return launch_decoder_i2t(q, half, stride, 384, 256, bi, s.kv_i2t, a1, 1, n, st);
   };
   // keys <- norm4(keys + out_proj(image->token attention))   (transformer.py:176-180)
-  auto keys_update = [&](int layer, const float* resid, int resid_mod, const int* row_img, void* out, int out_f16) -> int {
+  auto keys_update = [&](int layer, const void* resid, int resid_f16, int resid_mod, const int* row_img, void* out, int out_f16) -> int {
     const float *ob, *nw, *nb;
     INK_TRY(need_f32(h, T + std::to_string(layer) + ".cross_attn_image_to_token.out_proj.bias", &ob));
     INK_TRY(need_f32(h, T + std::to_string(layer) + ".norm4.weight", &nw));
     INK_TRY(need_f32(h, T + std::to_string(layer) + ".norm4.bias", &nb));
     G c; c.tf32 = 0; c.epi = EPI_RESID_LN_F32; c.A = a1; c.lda = 128; c.W = h->wo16[layer]; c.ldw = 128;
     c.g.ab_f16 = 1; c.g.out_f16 = out_f16;
-    c.g.M = Mb; c.g.N = 256; c.g.K = 128; c.g.ldo = 256; c.g.out = out; c.g.bias = ob; c.g.resid = resid;
+    c.g.M = Mb; c.g.N = 256; c.g.K = 128; c.g.ldo = 256; c.g.out = out; c.g.bias = ob; c.g.resid = static_cast<const float*>(resid);
+    c.g.resid_f16 = resid_f16;
     c.g.resid_mod = resid_mod; c.g.row_img = row_img; c.g.ln_w = nw; c.g.ln_b = nb; c.g.ln_eps = 1e-5f;
     return run_gemm(h, c, st);
   };
@@ -659,12 +661,12 @@ int decode_chunk(inksam_handle* h, const float* keys0, const float* kvq0, char* 
   INK_TRY(t2i(kvq0, 0, 4096LL * 384, 384, bimg));
   INK_TRY(tokens(2, 0));
   INK_TRY(i2t(kvq0, 0, 4096LL * 384, bimg));
-  INK_TRY(keys_update(0, keys0, 4096, bimg, keysb, 0));
+  INK_TRY(keys_update(0, keys0, 0, 4096, bimg, keysb, 1));  // layer-1 keys: fp16 [n][4096][256] (first half of keysb)
   // ---- layer 1: per-box keys
   {
-    G c; c.tf32 = 1; c.bn = 128; c.epi = EPI_BIAS_ROWADD_F32; c.A = keysb; c.lda = 256; c.W = h->wkvq[1]; c.ldw = 256;
+    G c; c.tf32 = 0; c.bn = 128; c.epi = EPI_BIAS_ROWADD_F32; c.A = keysb; c.lda = 256; c.W = h->wkvq16; c.ldw = 256;
     c.g.M = Mb; c.g.N = 384; c.g.K = 256; c.g.ldo = 384; c.g.out = kvq; c.g.bias = nullptr; c.g.rowadd = h->ra[1];
-    c.g.rowadd_mod = 4096; c.g.out_f16 = 1;
+    c.g.rowadd_mod = 4096; c.g.out_f16 = 1; c.g.ab_f16 = 1;
     INK_TRY(run_gemm(h, c, st));
   }
   INK_TRY(tokens(1, 1));
@@ -674,7 +676,7 @@ int decode_chunk(inksam_handle* h, const float* keys0, const float* kvq0, char* 
   // the final keys are fp16 only: [n][4096][256] halves in the upper half of the k|v|q buffer (layer 1's k|v|q are dead; the
   // final k|v and then the upscaled map go into its lower part)
   void* keys2 = reinterpret_cast<char*>(kvq) + (size_t)n * 4096 * 384 * 2;
-  INK_TRY(keys_update(1, keysb, 0, nullptr, keys2, 1));
+  INK_TRY(keys_update(1, keysb, 1, 0, nullptr, keys2, 1));
   // ---- final token -> image attention
   {
     G c; c.tf32 = 0; c.epi = EPI_BIAS_ROWADD_F32; c.A = keys2; c.lda = 256; c.W = h->wkvf16; c.ldw = 256;

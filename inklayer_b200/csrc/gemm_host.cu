@@ -237,6 +237,7 @@ int launch_gemm(int cg, int tf32, int bn, int epi, const void* A, int lda, const
   GEMM_CASE(1, 1, 128, EPI_UPSCALE2_MASK)
   GEMM_CASE(2, 1, 128, EPI_UPSCALE2_MASK)
   // 2-byte operands with the decoder's epilogues: fp16 GEMM-to-GEMM intermediates (GemmArgs::ab_f16)
+  GEMM_CASE(2, 0, 128, EPI_BIAS_ROWADD_F32)
   GEMM_CASE(2, 0, 256, EPI_RESID_LN_F32)
   GEMM_CASE(2, 0, 256, EPI_UPSCALE1)
   GEMM_CASE(2, 0, 128, EPI_UPSCALE2_MASK)

@@ -17,6 +17,7 @@
 //   image_encoder.py:88-104 (neck), :391-395 (patch embed), and the image-side linears of
 //   SA/modeling/transformer.py:218-221 and mask_decoder.py:53-59.
 #pragma once
+#include <cuda_fp16.h>
 #include "ptx.cuh"
 #include "gemm_args.h"
 
@@ -536,27 +537,44 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
         uint32_t rr[2][32];
         int mm = row_ok ? (g.resid_mod ? m % g.resid_mod : m) : 0;
         if (g.row_img != nullptr && row_ok) mm += __ldg(g.row_img + m / g.resid_mod) * g.resid_mod;
-        const float* rrow = g.resid + (size_t)mm * g.ldo;
+        // the residual rows are fp32, or fp16 (GemmArgs::resid_f16: 64 bytes per 32-column chunk)
+        const char* rrow = reinterpret_cast<const char*>(g.resid) + (size_t)mm * g.ldo * (g.resid_f16 ? 2 : 4);
+        auto load_resid = [&](int b, int c) {
+          if (g.resid_f16) {
 #pragma unroll
-        for (int h = 0; h < 4; ++h) ld_global_v8_stream(rrow + c_first * 32 + h * 8, *reinterpret_cast<uint32_t(*)[8]>(&rr[0][h * 8]));
+            for (int h = 0; h < 2; ++h)
+              ld_global_v8_stream(rrow + c * 64 + h * 32, *reinterpret_cast<uint32_t(*)[8]>(&rr[b][h * 8]));
+          } else {
+#pragma unroll
+            for (int h = 0; h < 4; ++h)
+              ld_global_v8_stream(rrow + c * 128 + h * 32, *reinterpret_cast<uint32_t(*)[8]>(&rr[b][h * 8]));
+          }
+        };
+        load_resid(0, c_first);
         float sum = 0.f, sq = 0.f;
 #pragma unroll
         for (int ci = 0; ci < NCW; ++ci) {
           const int c = c_first + ci;
           tmem_ld_32x32(taddr + c * 32, v);
-          if (ci + 1 < NCW) {
-#pragma unroll
-            for (int h = 0; h < 4; ++h)
-              ld_global_v8_stream(rrow + (c + 1) * 32 + h * 8, *reinterpret_cast<uint32_t(*)[8]>(&rr[(ci + 1) & 1][h * 8]));
-          }
+          if (ci + 1 < NCW) load_resid((ci + 1) & 1, c + 1);
           tmem_ld_wait();
+          if (g.resid_f16) {
 #pragma unroll
-          for (int j = 0; j < 32; j += 4) {
-            const float4 b4 = lds4c(econst + 4 * (c * 32 + j));
-            f[j] += b4.x + __uint_as_float(rr[ci & 1][j]);
-            f[j + 1] += b4.y + __uint_as_float(rr[ci & 1][j + 1]);
-            f[j + 2] += b4.z + __uint_as_float(rr[ci & 1][j + 2]);
-            f[j + 3] += b4.w + __uint_as_float(rr[ci & 1][j + 3]);
+            for (int j = 0; j < 32; j += 4) {
+              const float4 b4 = lds4c(econst + 4 * (c * 32 + j));
+              const float2 r0 = __half22float2(*reinterpret_cast<const __half2*>(&rr[ci & 1][j >> 1]));
+              const float2 r1 = __half22float2(*reinterpret_cast<const __half2*>(&rr[ci & 1][(j >> 1) + 1]));
+              f[j] += b4.x + r0.x; f[j + 1] += b4.y + r0.y; f[j + 2] += b4.z + r1.x; f[j + 3] += b4.w + r1.y;
+            }
+          } else {
+#pragma unroll
+            for (int j = 0; j < 32; j += 4) {
+              const float4 b4 = lds4c(econst + 4 * (c * 32 + j));
+              f[j] += b4.x + __uint_as_float(rr[ci & 1][j]);
+              f[j + 1] += b4.y + __uint_as_float(rr[ci & 1][j + 1]);
+              f[j + 2] += b4.z + __uint_as_float(rr[ci & 1][j + 2]);
+              f[j + 3] += b4.w + __uint_as_float(rr[ci & 1][j + 3]);
+            }
           }
           tmem_st_32x32(taddr + c * 32, v);
 #pragma unroll
