@@ -111,10 +111,10 @@ int inksam_op_gemm_rowadd_f16(int cg, int tf32, int bn, const void* A, int lda, 
  * inksam_op_gemm_f16: inksam_op_gemm with fp16 operands A [M][lda] and W [N][ldw] (kind::f16 MMAs, fp32 accumulation) for the
  * epilogues the decoder's fp16 intermediates go through -- epi 3 (row-add), 6 (residual + LayerNorm, N == bn == 256),
  * 8 (upscale 1, bn 256), 9 (upscale 2 + mask, bn 128); out_f16 != 0 stores the output as fp16 (epi 3, 6, 8); resid_f16 != 0:
- * the residual rows of epi 6 are fp16. */
+ * the residual rows of epi 6 are fp16; rowadd_f16 != 0: the row-add table of epi 3 is fp16. */
 int inksam_op_gemm_f16(int cg, int bn, int epi, const void* A, int lda, const void* W, int ldw, int M, int N, int K, void* out, int ldo,
-                       int out_f16, const float* bias, const void* resid, const float* rowadd, int rowadd_mod, const float* ln_w,
-                       const float* ln_b, float ln_eps, const float* hyper, int resid_mod, int resid_f16, void* stream);
+                       int out_f16, const float* bias, const void* resid, const void* rowadd, int rowadd_mod, const float* ln_w,
+                       const float* ln_b, float ln_eps, const float* hyper, int resid_mod, int resid_f16, int rowadd_f16, void* stream);
 
 /* ResizeLongestSide.apply_image on the device: Pillow's 8-bit bilinear resample (torchvision resize of a PIL image,
  * SA/utils/transforms.py:26-31; algorithm of Pillow libImaging/Resample.c), bit-exact with the host path.

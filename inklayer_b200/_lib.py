@@ -65,7 +65,7 @@ SIGNATURES = {
     "inksam_op_decoder_t2i": (c_int, [c_void_p, c_void_p, c_int, c_longlong, c_int, c_void_p, c_void_p, c_void_p, c_int, c_void_p]),
     "inksam_op_decoder_i2t": (c_int, [c_void_p, c_int, c_longlong, c_int, c_int, c_void_p, c_void_p, c_void_p, c_int, c_int, c_void_p]),
     "inksam_op_gemm_f16": (c_int, [c_int, c_int, c_int, c_void_p, c_int, c_void_p, c_int, c_int, c_int, c_int, c_void_p, c_int, c_int,
-                                   c_void_p, c_void_p, c_void_p, c_int, c_void_p, c_void_p, c_float, c_void_p, c_int, c_int, c_void_p]),
+                                   c_void_p, c_void_p, c_void_p, c_int, c_void_p, c_void_p, c_float, c_void_p, c_int, c_int, c_int, c_void_p]),
     "inksam_op_gemm_rowadd_f16": (c_int, [c_int, c_int, c_int, c_void_p, c_int, c_void_p, c_int, c_int, c_int, c_int, c_void_p, c_int,
                                           c_void_p, c_void_p, c_int, c_void_p]),
     "inksam_resize_workspace_bytes": (c_size_t, [c_int, c_int, c_int, c_int]),

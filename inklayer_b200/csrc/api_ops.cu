@@ -36,10 +36,11 @@ int inksam_op_gemm_rowadd_f16(int cg, int tf32, int bn, const void* A, int lda, 
 }
 
 int inksam_op_gemm_f16(int cg, int bn, int epi, const void* A, int lda, const void* W, int ldw, int M, int N, int K, void* out, int ldo,
-                       int out_f16, const float* bias, const void* resid, const float* rowadd, int rowadd_mod, const float* ln_w,
-                       const float* ln_b, float ln_eps, const float* hyper, int resid_mod, int resid_f16, void* stream) {
+                       int out_f16, const float* bias, const void* resid, const void* rowadd, int rowadd_mod, const float* ln_w,
+                       const float* ln_b, float ln_eps, const float* hyper, int resid_mod, int resid_f16, int rowadd_f16, void* stream) {
   GemmArgs g{};
-  g.M = M; g.N = N; g.K = K; g.ldo = ldo; g.out = out; g.bias = bias; g.resid = static_cast<const float*>(resid); g.rowadd = rowadd;
+  g.M = M; g.N = N; g.K = K; g.ldo = ldo; g.out = out; g.bias = bias; g.resid = static_cast<const float*>(resid);
+  g.rowadd = static_cast<const float*>(rowadd); g.rowadd_f16 = rowadd_f16;
   g.rowadd_mod = rowadd_mod; g.ln_w = ln_w; g.ln_b = ln_b; g.ln_eps = ln_eps; g.hyper = hyper; g.resid_mod = resid_mod;
   g.ab_f16 = 1; g.out_f16 = out_f16; g.resid_f16 = resid_f16;
   return launch_gemm(cg, 0, bn, epi, A, lda, W, ldw, g, device_sms(), static_cast<cudaStream_t>(stream));

@@ -48,6 +48,7 @@ struct inksam_handle {
   // fp16 copies of the weights whose A operand is an fp16 intermediate (GemmArgs::ab_f16): out_proj of the two image->token
   // attentions [256][128], the final k|v projection [256][256], the two transposed convolutions [256][256] / [128][64]
   void *wo16[2] = {nullptr, nullptr}, *wkvq16 = nullptr, *wkvf16 = nullptr, *up0_16 = nullptr, *up3_16 = nullptr;
+  void *ra16 = nullptr, *raf16 = nullptr;  // fp16 copies of the row-add tables ra[1] / raf (their sums are stored as fp16 anyway)
   // workspaces: sized once by inksam_reserve, otherwise grow-only.  A buffer that has to grow is RETIRED, not freed (work
   // already enqueued on any stream -- or baked into a captured CUDA graph -- may still use it); retired buffers are released
   // by inksam_reserve / inksam_destroy after a device synchronisation.  ws_generation counts reallocations so that the
@@ -365,6 +366,8 @@ int finalize_decoder(inksam_handle* h, cudaStream_t st) {
     INK_TRY(to_f16(ow, 256, 128, &h->wo16[l]));
   }
   INK_TRY(to_f16(h->wkvq[1], 384, 256, &h->wkvq16));
+  INK_TRY(to_f16(h->ra[1], 4096, 384, &h->ra16));
+  INK_TRY(to_f16(h->raf, 4096, 256, &h->raf16));
   INK_TRY(to_f16(h->wkvf, 256, 256, &h->wkvf16));
   {
     const float *u0w, *u3w;
@@ -665,7 +668,8 @@ int decode_chunk(inksam_handle* h, const float* keys0, const float* kvq0, char* 
   // ---- layer 1: per-box keys
   {
     G c; c.tf32 = 0; c.bn = 128; c.epi = EPI_BIAS_ROWADD_F32; c.A = keysb; c.lda = 256; c.W = h->wkvq16; c.ldw = 256;
-    c.g.M = Mb; c.g.N = 384; c.g.K = 256; c.g.ldo = 384; c.g.out = kvq; c.g.bias = nullptr; c.g.rowadd = h->ra[1];
+    c.g.M = Mb; c.g.N = 384; c.g.K = 256; c.g.ldo = 384; c.g.out = kvq; c.g.bias = nullptr;
+    c.g.rowadd = static_cast<const float*>(h->ra16); c.g.rowadd_f16 = 1;
     c.g.rowadd_mod = 4096; c.g.out_f16 = 1; c.g.ab_f16 = 1;
     INK_TRY(run_gemm(h, c, st));
   }
@@ -680,7 +684,8 @@ int decode_chunk(inksam_handle* h, const float* keys0, const float* kvq0, char* 
   // ---- final token -> image attention
   {
     G c; c.tf32 = 0; c.epi = EPI_BIAS_ROWADD_F32; c.A = keys2; c.lda = 256; c.W = h->wkvf16; c.ldw = 256;
-    c.g.M = Mb; c.g.N = 256; c.g.K = 256; c.g.ldo = 256; c.g.out = kvq; c.g.bias = nullptr; c.g.rowadd = h->raf;
+    c.g.M = Mb; c.g.N = 256; c.g.K = 256; c.g.ldo = 256; c.g.out = kvq; c.g.bias = nullptr;
+    c.g.rowadd = static_cast<const float*>(h->raf16); c.g.rowadd_f16 = 1;
     c.g.rowadd_mod = 4096; c.g.out_f16 = 1; c.g.ab_f16 = 1;
     INK_TRY(run_gemm(h, c, st));
   }

@@ -52,6 +52,7 @@ struct GemmArgs {
   int ab_f16;             // 2-byte operands (tf32 == 0) are fp16 instead of bf16 (the decoder's GEMM-to-GEMM intermediates; same 10
                           // explicit mantissa bits as the tf32 operands they replace, half the bytes)
   int resid_f16;          // EPI_RESID_LN_F32: the residual rows are fp16 [..][ldo]
+  int rowadd_f16;         // EPI_BIAS_ROWADD_F32: the row-add table is fp16 [rowadd_mod][N]
   int out_f16;            // EPI_BIAS_ROWADD_F32 / EPI_RESID_LN_F32 / EPI_UPSCALE1: store the output as fp16 (round to nearest,
                           // saturating) instead of fp32; same shape, ldo in elements.
                           // The decoder's per-box k|v|q are consumed once, by fp32 FMAs, after a tf32 GEMM produced them: fp16 keeps the

@@ -294,17 +294,21 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
       // same thread stores it, and no other thread touches it.
       uint32_t radd[kHasAdd ? 2 : 1][32];
       const float* add_row = nullptr;
+      constexpr bool kRowAdd = (EPI == EPI_BIAS_ROWADD_F32);
+      [[maybe_unused]] const __half* add_row16 = nullptr;  // GemmArgs::rowadd_f16
       if constexpr (kHasAdd) {
         const int mm = row_ok ? m : 0;
         if constexpr (epi_is_resid(EPI)) add_row = g.resid + (size_t)mm * g.ldo + n0;
         else add_row = g.rowadd + (size_t)(mm % g.rowadd_mod) * g.N + n0;
+        if constexpr (kRowAdd) add_row16 = reinterpret_cast<const __half*>(g.rowadd) + (size_t)(mm % g.rowadd_mod) * g.N + n0;
         if (n0 + c_first * 32 < g.N) {
 #pragma unroll
           for (int h = 0; h < 4; ++h) {
-            if constexpr (epi_is_resid(EPI))
+            if (kRowAdd && g.rowadd_f16) {  // fp16 table: 64 bytes per 32-column chunk
+              if (h < 2) ld_global_v8_stream(add_row16 + c_first * 32 + h * 16, *reinterpret_cast<uint32_t(*)[8]>(&radd[0][h * 8]));
+            } else {
               ld_global_v8_stream(add_row + c_first * 32 + h * 8, *reinterpret_cast<uint32_t(*)[8]>(&radd[0][h * 8]));
-            else
-              ld_global_v8_stream(add_row + c_first * 32 + h * 8, *reinterpret_cast<uint32_t(*)[8]>(&radd[0][h * 8]));
+            }
           }
         }
       }
@@ -478,8 +482,14 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
             if constexpr (kHasAdd) {
               if (ci + 1 < NCW && col + 32 < g.N) {
 #pragma unroll
-                for (int h = 0; h < 4; ++h)
-                  ld_global_v8_stream(add_row + (c + 1) * 32 + h * 8, *reinterpret_cast<uint32_t(*)[8]>(&radd[(ci + 1) & 1][h * 8]));
+                for (int h = 0; h < 4; ++h) {
+                  if (kRowAdd && g.rowadd_f16) {
+                    if (h < 2)
+                      ld_global_v8_stream(add_row16 + (c + 1) * 32 + h * 16, *reinterpret_cast<uint32_t(*)[8]>(&radd[(ci + 1) & 1][h * 8]));
+                  } else {
+                    ld_global_v8_stream(add_row + (c + 1) * 32 + h * 8, *reinterpret_cast<uint32_t(*)[8]>(&radd[(ci + 1) & 1][h * 8]));
+                  }
+                }
               }
             }
             tmem_ld_wait();
@@ -518,7 +528,16 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
             } else {
               if constexpr (kHasAdd) {
 #pragma unroll
-                for (int j = 0; j < 32; ++j) f[j] += __uint_as_float(radd[ci & 1][j]);
+                if (kRowAdd && g.rowadd_f16) {
+#pragma unroll
+                  for (int j = 0; j < 16; ++j) {
+                    const float2 r2 = __half22float2(*reinterpret_cast<const __half2*>(&radd[ci & 1][j]));
+                    f[2 * j] += r2.x; f[2 * j + 1] += r2.y;
+                  }
+                } else {
+#pragma unroll
+                  for (int j = 0; j < 32; ++j) f[j] += __uint_as_float(radd[ci & 1][j]);
+                }
               }
               if (EPI == EPI_BIAS_ROWADD_F32 && g.out_f16) {
                 stage_chunk_f16(f, col);

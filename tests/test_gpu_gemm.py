@@ -123,7 +123,7 @@ def test_upscale_epilogues(cg):
 
 
 def gemm_f16(epi, A, W, out, bn=256, out_f16=0, bias=None, resid=None, rowadd=None, rowadd_mod=1, ln_w=None, ln_b=None, eps=1e-6,
-             hyper=None, resid_mod=0, resid_f16=0):
+             hyper=None, resid_mod=0, resid_f16=0, rowadd_f16=0):
     import ctypes
     from gpu_util import ptr, stream
     from inklayer_b200 import _lib
@@ -132,7 +132,7 @@ def gemm_f16(epi, A, W, out, bn=256, out_f16=0, bias=None, resid=None, rowadd=No
     ldo = N
     _lib.check(_lib.load().inksam_op_gemm_f16(2, bn, epi, ptr(A), A.stride(0), ptr(W), W.stride(0), M, N, K, ptr(out), ldo, out_f16,
                                               ptr(bias), ptr(resid), ptr(rowadd), rowadd_mod, ptr(ln_w), ptr(ln_b), ctypes.c_float(eps),
-                                              ptr(hyper), resid_mod, resid_f16, stream()))
+                                              ptr(hyper), resid_mod, resid_f16, rowadd_f16, stream()))
 
 
 def test_fp16_operand_decoder_epilogues():
@@ -170,6 +170,9 @@ def test_fp16_operand_decoder_epilogues():
     o3 = torch.zeros(M, 384, device="cuda", dtype=torch.float16)
     gemm_f16(EPI["ROWADD"], A, Wq, o3, bn=128, out_f16=1, rowadd=radd3, rowadd_mod=4096)
     assert rel_err(o3, A.float() @ Wq.float().t() + radd3.repeat(n, 1)) < 6e-4
+    r3h = radd3.half()  # fp16 row-add table
+    gemm_f16(EPI["ROWADD"], A, Wq, o3, bn=128, out_f16=1, rowadd=r3h, rowadd_mod=4096, rowadd_f16=1)
+    assert rel_err(o3, A.float() @ Wq.float().t() + r3h.float().repeat(n, 1)) < 6e-4
     # the two transposed convolutions
     keysh = rnd(M, 256, seed=11).half()
     ct0 = rnd(256, 64, 2, 2, scale=0.06, seed=12); b0 = rnd(64, seed=13)
