@@ -328,6 +328,18 @@ __device__ __forceinline__ float fast_exp2(float x) {  // ex2.approx: one MUFU i
   return y;
 }
 
+// 4-term dot product and 4-wide axpy on fma.rn.f32x2 (the attention kernels below are issue-bound)
+__device__ __forceinline__ float dot4_f2(const float4& a, const float4& b) {
+  float lo, hi;
+  f2_unpack(f2_fma(f2_pack(a.z, a.w), f2_pack(b.z, b.w), f2_mul(f2_pack(a.x, a.y), f2_pack(b.x, b.y))), lo, hi);
+  return lo + hi;
+}
+__device__ __forceinline__ void axpy4_f2(float4& acc, float p, const float4& v) {
+  const uint64_t p2 = f2_pack(p, p);
+  f2_unpack(f2_fma(p2, f2_pack(v.x, v.y), f2_pack(acc.x, acc.y)), acc.x, acc.y);
+  f2_unpack(f2_fma(p2, f2_pack(v.z, v.w), f2_pack(acc.z, acc.w)), acc.z, acc.w);
+}
+
 constexpr int T2I_SPLITS = 8;                       // key ranges per box
 constexpr int T2I_PART = 8 * NT * 18;               // floats of one partial: [head][token][16 acc, l, m]
 
@@ -382,7 +394,7 @@ __global__ void __launch_bounds__(256) decoder_t2i_kernel(const float* __restric
 #pragma unroll
   for (int t = 0; t < NT; ++t) {  // the shift of a token starts at its score with this warp's first key
     const float4 k0 = cvt_row4(nk[0]);
-    float x = q4[t].x * k0.x + q4[t].y * k0.y + q4[t].z * k0.z + q4[t].w * k0.w;
+    float x = dot4_f2(q4[t], k0);
     x += __shfl_xor_sync(0xffffffffu, x, 1);
     x += __shfl_xor_sync(0xffffffffu, x, 2);
     m[t] = x;
@@ -397,7 +409,7 @@ __global__ void __launch_bounds__(256) decoder_t2i_kernel(const float* __restric
     float sc[NT], over = -INFINITY;
 #pragma unroll
     for (int t = 0; t < NT; ++t) {
-      float x = q4[t].x * kk.x + q4[t].y * kk.y + q4[t].z * kk.z + q4[t].w * kk.w;
+      float x = dot4_f2(q4[t], kk);
       x += __shfl_xor_sync(0xffffffffu, x, 1);
       x += __shfl_xor_sync(0xffffffffu, x, 2);  // the four lanes of a head hold the same score
       sc[t] = x - m[t];
@@ -419,7 +431,7 @@ __global__ void __launch_bounds__(256) decoder_t2i_kernel(const float* __restric
     for (int t = 0; t < NT; ++t) {
       const float p = fast_exp2(sc[t]);
       l[t] += p;
-      acc[t].x += p * vv.x; acc[t].y += p * vv.y; acc[t].z += p * vv.z; acc[t].w += p * vv.w;
+      axpy4_f2(acc[t], p, vv);
     }
   }
   // merge the 8 warps (each holds the softmax state of its 64 keys for every head and token)
@@ -541,7 +553,7 @@ __global__ void __launch_bounds__(256) decoder_i2t_kernel(const void* __restrict
     float sc[NT], mx = -INFINITY;
 #pragma unroll
     for (int t = 0; t < NT; ++t) {
-      float x = q.x * k4[t].x + q.y * k4[t].y + q.z * k4[t].z + q.w * k4[t].w;
+      float x = dot4_f2(q, k4[t]);
       x += __shfl_xor_sync(0xffffffffu, x, 1);
       x += __shfl_xor_sync(0xffffffffu, x, 2);  // all four lanes of the head hold the same sum
       sc[t] = x;
@@ -554,8 +566,7 @@ __global__ void __launch_bounds__(256) decoder_i2t_kernel(const void* __restrict
     float4 o = make_float4(0.f, 0.f, 0.f, 0.f);
 #pragma unroll
     for (int t = 0; t < NT; ++t) {
-      const float p = sc[t] * inv;
-      o.x += p * v4[t].x; o.y += p * v4[t].y; o.z += p * v4[t].z; o.w += p * v4[t].w;
+      axpy4_f2(o, sc[t] * inv, v4[t]);
     }
     if constexpr (OUT_HALF) {
       uint2 h2;
