@@ -86,7 +86,8 @@ struct GemmCfg {
   static constexpr int B_BYTES = BNL * 128;
   static constexpr int STAGE_BYTES = A_BYTES + B_BYTES;
   static constexpr int STAGING_BYTES = ST ? 8 * 2 * 2048 : 0;
-  static constexpr int AUX_BYTES = ST == 1 ? 256 /*barriers*/ : 256 /*barriers*/ + 4096 /*LN partials*/ + 3072 /*epilogue constants*/;
+  static constexpr int AUX_BYTES = ST == 1 ? 256 /*barriers*/ + 1024 /*the tile's bias slice (fp32 residual epilogue)*/
+                                           : 256 /*barriers*/ + 4096 /*LN partials*/ + 3072 /*epilogue constants*/;
   static constexpr int RING_BUDGET = ST ? (227 * 1024 - 1024 - AUX_BYTES - STAGING_BYTES) : 192 * 1024;
   static constexpr int STAGES = RING_BUDGET / STAGE_BYTES > 8 ? 8 : RING_BUDGET / STAGE_BYTES;
   static constexpr int KELEMS = TF32 ? 32 : 64;  // elements per 128-byte smem row
@@ -328,6 +329,19 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
         rstd2 = f2_pack(rstd, rstd);
         nrm2 = f2_pack(-rstd * mean, -rstd * mean);
       }
+      // fp32 residual epilogue: the BN bias values of this tile go through shared memory.  As __ldg loads inside the chunk loop
+      // they queued behind the streaming residual loads (32 sectors per instruction) and the add that consumes them was the
+      // hottest stall of the short-K attn.proj GEMM (17 % of the epilogue warps' samples, ncu).  One value per epilogue thread,
+      // fetched before the accumulator wait; two named barriers per tile keep the single 1 KB slice consistent.
+      [[maybe_unused]] const uint32_t bias_smem = bar_base + 256;
+      if constexpr (epi_is_resid(EPI)) {
+        const int bi = (int)threadIdx.x - 128;  // 0..255: column of the tile
+        float bv = 0.f;
+        if (g.bias != nullptr && n0 + bi < g.N) bv = __ldg(g.bias + n0 + bi);
+        named_bar_sync(9, 256);  // every epilogue warp is done with the previous tile's slice
+        asm volatile("st.shared.f32 [%0], %1;" ::"r"(bias_smem + 4u * (uint32_t)bi), "f"(bv) : "memory");
+        named_bar_sync(9, 256);
+      }
       mbar_wait(tfull_bar(as), aphase);
       tc_fence_after();
 
@@ -420,8 +434,7 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
                 const int e = hf * 16 + 4 * j;          // column of the chunk
                 // bias: broadcast 16-byte loads that stay in L1 (the residual stream bypasses it); the two adds run on
                 // pairs (add.rn.f32x2): (acc + bias) + resid, the order of the unfused reference
-                float4 b4 = make_float4(0.f, 0.f, 0.f, 0.f);
-                if (g.bias != nullptr) b4 = __ldg(reinterpret_cast<const float4*>(g.bias + col + e));
+                const float4 b4 = lds4c(bias_smem + 4u * (uint32_t)(c * 32 + e));  // the tile's bias slice (staged above)
                 float x0, x1, x2, x3;
                 f2_unpack(f2_add(f2_add(f2_pack(f[e], f[e + 1]), f2_pack(b4.x, b4.y)),
                                  f2_pack(__uint_as_float(radd[ci & 1][e]), __uint_as_float(radd[ci & 1][e + 1]))), x0, x1);
