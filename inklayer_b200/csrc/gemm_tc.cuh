@@ -334,6 +334,15 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
       // hottest stall of the short-K attn.proj GEMM (17 % of the epilogue warps' samples, ncu).  One value per epilogue thread,
       // fetched before the accumulator wait; two named barriers per tile keep the single 1 KB slice consistent.
       [[maybe_unused]] const uint32_t bias_smem = bar_base + 256;
+      if constexpr (epi_is_fold(EPI)) {  // the same for the folded-LayerNorm epilogues: bias and column sums of the tile
+        const int bi = (int)threadIdx.x - 128;
+        float bv = 0.f, cv = 0.f;
+        if (n0 + bi < g.N) { bv = __ldg(g.bias + n0 + bi); cv = __ldg(g.colsum + n0 + bi); }
+        named_bar_sync(9, 256);
+        asm volatile("st.shared.f32 [%0], %1;" ::"r"(econst + 4u * (uint32_t)bi), "f"(bv) : "memory");
+        asm volatile("st.shared.f32 [%0], %1;" ::"r"(econst + 4u * (uint32_t)(256 + bi)), "f"(cv) : "memory");
+        named_bar_sync(9, 256);
+      }
       if constexpr (epi_is_resid(EPI)) {
         const int bi = (int)threadIdx.x - 128;  // 0..255: column of the tile
         float bv = 0.f;
@@ -509,8 +518,8 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
             if constexpr (fold) {
 #pragma unroll
               for (int j = 0; j < 32; j += 4) {
-                const float4 b4 = __ldg(reinterpret_cast<const float4*>(g.bias + col + j));
-                const float4 c4 = __ldg(reinterpret_cast<const float4*>(g.colsum + col + j));
+                const float4 b4 = lds4c(econst + 4u * (uint32_t)(c * 32 + j));          // the tile's bias / column-sum slices
+                const float4 c4 = lds4c(econst + 4u * (uint32_t)(256 + c * 32 + j));    // (staged before the accumulator wait)
                 f2_unpack(f2_fma(rstd2, f2_pack(f[j], f[j + 1]), f2_fma(nrm2, f2_pack(c4.x, c4.y), f2_pack(b4.x, b4.y))), f[j], f[j + 1]);
                 f2_unpack(f2_fma(rstd2, f2_pack(f[j + 2], f[j + 3]), f2_fma(nrm2, f2_pack(c4.z, c4.w), f2_pack(b4.z, b4.w))), f[j + 2],
                           f[j + 3]);
