@@ -41,6 +41,13 @@ int inksam_op_gemm(int cg, int tf32, int bn, int epi, const void* A, int lda, co
                    int rowadd_mod, const float* ln_w, const float* ln_b, float ln_eps, const float* hyper,
                    int a_conv3x3, int conv_c, int win_remap, int resid_mod, void* stream);
 
+/* qkv projection of a windowed encoder block as the engine launches it (CTA pairs, bias + bf16 epilogue with win_remap): A bf16
+ * [B*4096][lda] in natural token order, W bf16 [N][ldw]; out bf16 [B*25*196][N] in 14x14-window order.  pad_bias != null: the
+ * rows of the 804 padded window tokens per image are filled with bf16(pad_bias[N]) by the GEMM's epilogue warps (what
+ * inksam_op_fill_pad_rows does as a kernel of its own); null: they are left untouched. */
+int inksam_op_gemm_qkv_windowed(const void* A, int lda, const void* W, int ldw, int B, int N, int K, void* out, const float* bias,
+                                const float* pad_bias, void* stream);
+
 /* Encoder attention for B images: softmax(q k^T * hd^-0.5 + decomposed rel-pos bias) v, all heads
  * (SA/modeling/image_encoder.py:224-240,325-361).  windowed == 0: qkv is bf16 [B*4096][3*D] in token order and rel is
  * the bf16 table [256][hd] (rows 0..126 rel_pos_h, 128..254 rel_pos_w).  windowed == 1: qkv is bf16 [B*25*196][3*D] in

@@ -46,6 +46,13 @@ int inksam_op_gemm_f16(int cg, int bn, int epi, const void* A, int lda, const vo
   return launch_gemm(cg, 0, bn, epi, A, lda, W, ldw, g, device_sms(), static_cast<cudaStream_t>(stream));
 }
 
+int inksam_op_gemm_qkv_windowed(const void* A, int lda, const void* W, int ldw, int B, int N, int K, void* out, const float* bias,
+                                const float* pad_bias, void* stream) {
+  GemmArgs g{};
+  g.M = B * 4096; g.N = N; g.K = K; g.ldo = N; g.out = out; g.bias = bias; g.win_remap = 1; g.pad_bias = pad_bias; g.pad_images = B;
+  return launch_gemm(2, 0, 256, EPI_BIAS_BF16, A, lda, W, ldw, g, device_sms(), static_cast<cudaStream_t>(stream));
+}
+
 int inksam_op_attention(int windowed, const void* qkv, const void* rel, void* out, int B, int heads, int head_dim, void* stream) {
   return launch_attention(windowed, qkv, rel, out, B, heads, head_dim, static_cast<cudaStream_t>(stream));
 }

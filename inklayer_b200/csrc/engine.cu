@@ -512,12 +512,17 @@ int encode_chunk(inksam_handle* h, const void* images, int dtype, int B, const i
     {
       G c; c.epi = EPI_FOLD_BF16; c.A = xn; c.lda = D; c.W = b.qkv_w; c.ldw = D;
       c.g.M = M; c.g.N = 3 * D; c.g.K = D; c.g.ldo = 3 * D; c.g.out = qkv; c.g.bias = b.qkv_bf; c.g.win_remap = b.global ? 0 : 1;
+      // The padded window tokens' rows (q / k / v = the bare bias): at small batch this GEMM's epilogue warps write them while the
+      // first tile's MMAs run (ViT-H batch 1: 6.75 -> 6.63 ms per encode); at batch 8 that measured 1 % SLOWER than the separate
+      // 10 us kernel (44.45 -> 44.9 ms, same box: the step is power-capped and the extra stores delay the first epilogue).
+      const bool fuse_pad = !b.global && B <= 2;
+      if (fuse_pad) { c.g.pad_bias = b.qkv_b; c.g.pad_images = B; }
       c.g.stats_in = stats; c.g.colsum = b.qkv_cs; c.g.stats_np = np_in; c.g.fold_eps = 1e-6f;
       INK_TRY(run_gemm(h, c, st));
-    }
-    if (!b.global) {
-      ++h->launches;
-      INK_TRY(launch_fill_pad_rows(qkv, b.qkv_b, B, 3 * D, st));
+      if (!b.global && !fuse_pad) {
+        ++h->launches;
+        INK_TRY(launch_fill_pad_rows(qkv, b.qkv_b, B, 3 * D, st));
+      }
     }
     ++h->launches;
     {

@@ -37,6 +37,8 @@ struct GemmArgs {
   int conv_c;
   const float* hyper;  // EPI_UPSCALE2_MASK: [boxes][32]
   int win_remap;       // EPI_BIAS_BF16: store token rows in 14x14-window order (windowed encoder blocks)
+  const float* pad_bias;  // with win_remap: fp32 [N]; the epilogue warps also fill the rows of the padded window tokens (804 per image,
+  int pad_images;         // encoder_ops.cu fill_pad_rows_kernel) with bf16(pad_bias) while the first tile's MMAs run.  Null: not filled.
   int resid_mod;       // EPI_RESID_LN_F32: resid row = m % resid_mod when non-zero (keys shared by all boxes)
   const int* row_img;  // EPI_RESID_LN_F32 with resid_mod: resid row += row_img[m / resid_mod] * resid_mod (keys of the box's image)
   // LayerNorm folded into the GEMMs either side of it (encoder blocks).  The producer of the residual

@@ -271,6 +271,28 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
     int as = 0;
     uint32_t aphase = 0;
     uint32_t sk = 0;  // EPI_BIAS_RESID_STATS_F32 / fp16 output: running count of this warp's TMA stores (staging buffer = sk & 1)
+    // Windowed encoder blocks: q / k / v of a padded window token are the bare bias (the reference pads AFTER norm1 with zeros,
+    // image_encoder.py:169-173,243-264).  Those 804 rows per image used to be written by a kernel of their own between this GEMM
+    // and the attention (10 us x 28 blocks); the epilogue warps are idle until the first tile's accumulator is complete
+    // (~5 us), so they write them here: 16-byte stores, consecutive threads on consecutive columns of a row.
+    if constexpr (EPI == EPI_FOLD_BF16 || EPI == EPI_BIAS_BF16) {
+      if (g.win_remap && g.pad_bias != nullptr) {
+        const int groups = g.N >> 3;  // 16-byte column groups per row
+        const long long items = (long long)g.pad_images * 804 * groups;
+        for (long long it = (long long)blockIdx.x * 256 + ((int)threadIdx.x - 128); it < items; it += (long long)gridDim.x * 256) {
+          const int cg = (int)(it % groups);
+          const int rp = (int)(it / groups);
+          const int p = rp % 804, b = rp / 804;
+          // p: the 6 bottom rows of the padded 70x70 grid (420 tokens), then the 6 right columns of the other 64 rows
+          const int y = p < 420 ? 64 + p / 70 : (p - 420) / 6, x = p < 420 ? p % 70 : 64 + (p - 420) % 6;
+          const size_t row = (size_t)(b * 25 + (y / 14) * 5 + x / 14) * 196 + (y % 14) * 14 + x % 14;
+          const float4 f0 = __ldg(reinterpret_cast<const float4*>(g.pad_bias + cg * 8));
+          const float4 f1 = __ldg(reinterpret_cast<const float4*>(g.pad_bias + cg * 8 + 4));
+          st_global_v4(reinterpret_cast<__nv_bfloat16*>(g.out) + row * g.ldo + cg * 8, pack_bf16x2(f0.x, f0.y), pack_bf16x2(f0.z, f0.w),
+                       pack_bf16x2(f1.x, f1.y), pack_bf16x2(f1.z, f1.w));
+        }
+      }
+    }
     for (int tile = cluster_id; tile < num_tiles; tile += num_clusters) {
       const int m_blk = tile / tiles_n, n_blk = tile % tiles_n;
       const int m = m_blk * C::BM * CG + (int)rank * C::BM + q * 32 + lane;

@@ -200,3 +200,21 @@ def _same_as_fp32_then_half(a1, wo, bo, resid, lw, lb):
     k32 = torch.zeros(a1.shape[0], 256, device="cuda")
     gemm_f16(EPI["RESID_LN"], a1, wo, k32, bias=bo, resid=resid, ln_w=lw, ln_b=lb, eps=1e-5)
     return k32.half()
+
+
+def test_windowed_qkv_gemm_fills_the_padded_token_rows():
+    """The qkv GEMM of a windowed block also writes the rows of the padded window tokens (bf16 of the bare bias): identical to
+    the plain GEMM followed by inksam_op_fill_pad_rows."""
+    from gpu_util import ptr, stream
+    from inklayer_b200 import _lib
+    lib = _lib.load()
+    B, N, K = 2, 3840, 256
+    A = rnd(B * 4096, K, seed=1).bfloat16(); W = rnd(N, K, scale=0.05, seed=2).bfloat16()
+    bias = rnd(N, seed=3); pad_bias = rnd(N, seed=4)
+    want = torch.full((B * 25 * 196, N), 99.0, device="cuda", dtype=torch.bfloat16)
+    _lib.check(lib.inksam_op_gemm_qkv_windowed(ptr(A), K, ptr(W), K, B, N, K, ptr(want), ptr(bias), None, stream()))
+    assert (want == 99.0).any()  # padded rows untouched without pad_bias
+    _lib.check(lib.inksam_op_fill_pad_rows(ptr(want), ptr(pad_bias), B, N, stream()))
+    got = torch.full((B * 25 * 196, N), 99.0, device="cuda", dtype=torch.bfloat16)
+    _lib.check(lib.inksam_op_gemm_qkv_windowed(ptr(A), K, ptr(W), K, B, N, K, ptr(got), ptr(bias), ptr(pad_bias), stream()))
+    assert torch.equal(got, want)
