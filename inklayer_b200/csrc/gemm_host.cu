@@ -187,7 +187,7 @@ int launch_gemm(int cg, int tf32, int bn, int epi, const void* A, int lda, const
     return set_error("gemm: fp16 output is built for the row-add, residual + LayerNorm and upscale-1 epilogues only (epi=%d)", epi);
   if (g.ab_f16 && tf32) return set_error("gemm: fp16 operands go with tf32 = 0");
   CUtensorMap tO = tA;  // only the staged fp32 epilogues store through a tensor map
-  if (gemm_staged(epi) && !g.out_f16) {
+  if ((gemm_staged(epi) == 1 || gemm_staged(epi) == 2) && !g.out_f16) {
     if ((reinterpret_cast<uintptr_t>(g.out) & 15) != 0 || (g.ldo * 4) % 16 != 0)
       return set_error("gemm: epilogue %d stores its fp32 output by TMA and needs a 16-byte aligned output (ldo=%d)", epi, g.ldo);
     if (make_tmap_f32_out(&tO, g.out, g.M, g.N, g.ldo)) return -1;
@@ -197,6 +197,11 @@ int launch_gemm(int cg, int tf32, int bn, int epi, const void* A, int lda, const
     if ((reinterpret_cast<uintptr_t>(g.xb_out) & 15) != 0 || (g.ldo * 2) % 16 != 0)
       return set_error("gemm: the bf16 copy needs a 16-byte aligned xb_out (ldo=%d)", g.ldo);
     if (make_tmap_bf16_out(&tX, g.xb_out, g.M, g.N, g.ldo)) return -1;
+  }
+  if (gemm_staged(epi) == 3 && !g.win_remap) {
+    if ((reinterpret_cast<uintptr_t>(g.out) & 15) != 0 || (g.ldo * 2) % 16 != 0)
+      return set_error("gemm: the bf16 output is stored by TMA and needs a 16-byte aligned out (ldo=%d)", g.ldo);
+    if (make_tmap_bf16_out(&tX, g.out, g.M, g.N, g.ldo)) return -1;
   }
   if (g.out_f16 && epi != EPI_UPSCALE1) {
     if ((reinterpret_cast<uintptr_t>(g.out) & 15) != 0 || (g.ldo * 2) % 16 != 0)

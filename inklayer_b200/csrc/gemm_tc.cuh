@@ -85,7 +85,7 @@ struct GemmCfg {
   static constexpr int A_BYTES = BM * 128;       // one stage of A: 128 rows x 128 bytes
   static constexpr int B_BYTES = BNL * 128;
   static constexpr int STAGE_BYTES = A_BYTES + B_BYTES;
-  static constexpr int STAGING_BYTES = ST ? 8 * 2 * 2048 : 0;
+  static constexpr int STAGING_BYTES = ST == 3 ? 8 * 2048 : (ST ? 8 * 2 * 2048 : 0);  // ST == 3: one 2 KB buffer per epilogue warp
   static constexpr int AUX_BYTES = ST == 1 ? 256 /*barriers*/ + 1024 /*the tile's bias slice (fp32 residual epilogue)*/
                                            : 256 /*barriers*/ + 4096 /*LN partials*/ + 3072 /*epilogue constants*/;
   static constexpr int RING_BUDGET = ST ? (227 * 1024 - 1024 - AUX_BYTES - STAGING_BYTES) : 192 * 1024;
@@ -102,7 +102,12 @@ __host__ __device__ constexpr bool epi_is_fold(int epi) { return epi == EPI_FOLD
 // different lines into every instruction and held the decoder's image-side GEMMs at 70 % L1/LSU throughput and 38-49 % of
 // the HBM peak (ncu, round 2).
 __host__ __device__ constexpr int gemm_staged(int epi) {
-  return (epi_is_resid(epi) || epi == EPI_BIAS_ROWADD_F32 || epi == EPI_BIAS_F32) ? 1 : (epi == EPI_RESID_LN_F32 ? 2 : 0);
+  return (epi_is_resid(epi) || epi == EPI_BIAS_ROWADD_F32 || epi == EPI_BIAS_F32) ? 1
+         : epi == EPI_RESID_LN_F32 ? 2
+         // bf16 row-major outputs (qkv of the global blocks, mlp.lin1): one staging buffer per warp (the 6-stage ring and the
+         // epilogue constants leave room for 16 KB).  In the step, mlp.lin1 with its thread-per-row stores removed ran 110 us
+         // per launch faster (tools/encoder_ab.py): 32 sectors of 32 lines per store instruction again.
+         : (epi == EPI_BIAS_BF16 || epi == EPI_BIAS_GELU_BF16 || epi_is_fold(epi)) ? 3 : 0;
 }
 
 template <int CG, int TF32, int BN, int EPI>
@@ -428,6 +433,27 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
         }
       };
 
+      // bf16 output through the warp's single 2 KB staging buffer (ST == 3): 32 rows x 64 bytes, one TMA store per chunk
+      [[maybe_unused]] auto stage_chunk_bf16 = [&](const float* x, int col) {
+        uint32_t pk[16];
+#pragma unroll
+        for (int j = 0; j < 16; ++j) pk[j] = pack_bf16x2(x[2 * j], x[2 * j + 1]);
+        const uint32_t sb = staging_base + (uint32_t)(warp - 4) * 2048u;
+        const uint32_t srow = (uint32_t)lane * 64u, sx = (uint32_t)((lane >> 1) & 3);
+        if (lane == 0) bulk_wait_group_read<0>();  // the previous chunk's store has read the buffer
+        __syncwarp();
+#pragma unroll
+        for (int j = 0; j < 4; ++j)
+          st_shared_v4(sb + srow + (((uint32_t)j ^ sx) << 4), __uint_as_float(pk[4 * j]), __uint_as_float(pk[4 * j + 1]),
+                       __uint_as_float(pk[4 * j + 2]), __uint_as_float(pk[4 * j + 3]));
+        fence_proxy_async_smem();
+        __syncwarp();
+        if (lane == 0) {
+          tma_store_2d(&tmX, sb, col, m - lane);
+          bulk_commit_group();
+        }
+      };
+
       if constexpr (epi_is_resid(EPI)) {
         // out = resid + acc + bias, fp32.  Thread-per-row global stores of a 32 x 32 fp32 sub-tile touch 32 lines per
         // instruction; instead each warp writes 32 x 16 halves into 64B-swizzled staging buffers (conflict-free 16-byte
@@ -559,7 +585,9 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
               for (int j = 0; j < 32; j += 2) gelu_erf2(f[j], f[j + 1]);
             }
             if constexpr (EPI == EPI_BIAS_BF16 || EPI == EPI_BIAS_GELU_BF16 || fold) {
-              if (row_ok) {
+              if (!g.win_remap) {  // (window-order rows are not contiguous: thread-per-row stores below)
+                stage_chunk_bf16(f, col);
+              } else if (row_ok) {
                 __nv_bfloat16* o = reinterpret_cast<__nv_bfloat16*>(g.out) + (size_t)mo * g.ldo + col;
 #pragma unroll
                 for (int h = 0; h < 2; ++h) {
